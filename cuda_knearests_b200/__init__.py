@@ -1,0 +1,264 @@
+"""cuda_knearests_b200 -- ctypes binding of the B200-native exact kNN engine.
+
+The product is the C/C++/CUDA library ``libknearests_b200.so`` (sources in ``csrc/``, headers in
+``include/``); the reference is compiled code, so its host side is C++ too (``csrc/api.cu``).  This
+module is only the thin Python door that tests, ``bench.py`` and Python callers use: it mirrors the
+reference interface one to one (``knearests.h``: kn_prepare / kn_solve / kn_get_points /
+kn_get_knearests / kn_get_permutation / kn_print_stats / kn_free) and adds nothing to the data path.
+
+There is NO fallback: if the shared library is missing or no GPU is usable, calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import numpy as np
+
+HERE = Path(__file__).resolve().parent
+LIB_PATH = HERE / "libknearests_b200.so"
+EMPTY = 0xFFFFFFFF
+MAX_K = 256
+
+# every symbol include/knearests_c.h declares (tests check that the library exports all of them)
+C_ABI_SYMBOLS = [
+    "knc_prepare", "knc_prepare_ex", "knc_solve", "knc_free", "knc_get_points", "knc_get_permutation",
+    "knc_get_knearests", "knc_get_knearests_original", "knc_get_stats", "knc_get_info", "knc_get_timings",
+    "knc_grid_dim", "knc_last_error", "knc_version", "knc_generate_uniform_device",
+]
+# the reference's own (C++-mangled) entry points, knearests.h:21-29
+CXX_ABI_SYMBOLS = [
+    "_Z10kn_prepareP6float3i", "_Z8kn_solveP10kn_problem", "_Z7kn_freePP10kn_problem",
+    "_Z13kn_get_pointsP10kn_problem", "_Z16kn_get_knearestsP10kn_problem",
+    "_Z18kn_get_permutationP10kn_problem", "_Z14kn_print_statsP10kn_problem",
+]
+
+
+class KnError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"knearests_b200 error {code}: {message}")
+        self.code = code
+
+
+class Options(C.Structure):  # knc_options
+    _fields_ = [("struct_size", C.c_size_t), ("k", C.c_int), ("density", C.c_float),
+                ("points_on_device", C.c_int), ("grid_dim", C.c_int), ("z_begin", C.c_int),
+                ("z_end", C.c_int), ("own_z_begin", C.c_int), ("own_z_end", C.c_int),
+                ("search_scale", C.c_float)]
+
+
+class Info(C.Structure):  # knc_info
+    _fields_ = [("n", C.c_int), ("k", C.c_int), ("dimx", C.c_int), ("dimy", C.c_int), ("dimz", C.c_int),
+                ("z_begin", C.c_int), ("z_end", C.c_int), ("query_begin", C.c_int), ("query_count", C.c_int),
+                ("solved", C.c_int), ("d_points", C.c_void_p), ("d_points4", C.c_void_p),
+                ("d_permutation", C.c_void_p), ("d_counters", C.c_void_p), ("d_ptrs", C.c_void_p),
+                ("d_knearests", C.c_void_p)]
+
+
+class Stats(C.Structure):  # knc_stats
+    _fields_ = [("cells", C.c_longlong), ("min_per_cell", C.c_int), ("max_per_cell", C.c_int),
+                ("avg_per_cell", C.c_double), ("total", C.c_longlong), ("histogram", C.c_longlong * 64)]
+
+
+class Timings(C.Structure):  # knc_timings
+    _fields_ = [("build_ms", C.c_float), ("solve_ms", C.c_float), ("h2d_ms", C.c_float),
+                ("restarts", C.c_uint), ("max_radius2", C.c_float)]
+
+
+def build(verbose: bool = False) -> Path:
+    """Compile libknearests_b200.so for sm_100a in-tree (nvcc cross-compiles without a GPU)."""
+    subprocess.run(["make", "-C", str(HERE / "csrc")], check=True,
+                   stdout=None if verbose else subprocess.DEVNULL)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load the CUDA library.  Raises if it has not been built: there is no other implementation."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.exists():
+            raise ImportError(f"{LIB_PATH} is missing -- build it with `python -c 'import __graft_entry__ as g; "
+                              f"g.build()'` or `make -C cuda_knearests_b200/csrc`; there is no CPU fallback")
+        L = C.CDLL(str(LIB_PATH))
+        vp = C.c_void_p
+        L.knc_prepare.argtypes = [vp, C.c_int, C.c_int, C.POINTER(vp)]
+        L.knc_prepare_ex.argtypes = [vp, C.c_int, C.POINTER(Options), C.POINTER(vp)]
+        for nm in ("knc_solve", "knc_free"):
+            getattr(L, nm).argtypes = [vp]
+        for nm in ("knc_get_points", "knc_get_permutation", "knc_get_knearests", "knc_get_knearests_original"):
+            getattr(L, nm).argtypes = [vp, vp]
+        L.knc_get_stats.argtypes = [vp, C.POINTER(Stats)]
+        L.knc_get_info.argtypes = [vp, C.POINTER(Info)]
+        L.knc_get_timings.argtypes = [vp, C.POINTER(Timings)]
+        L.knc_grid_dim.argtypes = [C.c_int, C.c_float]
+        L.knc_generate_uniform_device.argtypes = [vp, C.c_longlong, C.c_longlong, C.c_uint64]
+        L.knc_last_error.restype = C.c_char_p
+        L.knc_version.restype = C.c_char_p
+        _lib = L
+    return _lib
+
+
+def _check(rc: int) -> None:
+    if rc != 0:
+        raise KnError(rc, lib().knc_last_error().decode())
+
+
+def grid_dim(n: int, density: float = 3.1) -> int:
+    return int(lib().knc_grid_dim(int(n), float(density)))
+
+
+def version() -> str:
+    return lib().knc_version().decode()
+
+
+class KnProblem:
+    """One point cloud on one GPU -- the reference's ``kn_problem`` handle (knearests.h:3-16).
+
+    ``points`` is either a host array (anything numpy can view as float32 [n,3]; copied to the device,
+    as kn_prepare does, knearests.cu:308-311) or a CUDA ``torch.Tensor`` float32 [n,3] (used in place).
+    """
+
+    def __init__(self, points, k: int = 0, density: float = 0.0, grid_dim: int = 0, slab=None,
+                 search_scale: float = 0.0):
+        self._h = C.c_void_p()
+        opt = Options()
+        opt.struct_size = C.sizeof(Options)
+        opt.k = int(k)
+        opt.density = float(density)
+        opt.grid_dim = int(grid_dim)
+        opt.search_scale = float(search_scale)
+        if slab is not None:
+            opt.z_begin, opt.z_end, opt.own_z_begin, opt.own_z_end = (int(v) for v in slab)
+        if hasattr(points, "is_cuda"):
+            import torch
+            if not points.is_cuda or points.dtype != torch.float32 or not points.is_contiguous():
+                raise ValueError("device input must be a contiguous CUDA float32 tensor [n,3]")
+            torch.cuda.current_stream(points.device).synchronize()  # the library works on its own stream
+            n = points.numel() // 3
+            opt.points_on_device = 1
+            self._keep = points
+            ptr = C.c_void_p(points.data_ptr())
+        else:
+            arr = np.ascontiguousarray(points, np.float32).reshape(-1, 3)
+            n = arr.shape[0]
+            self._keep = arr
+            ptr = C.c_void_p(arr.ctypes.data)
+        _check(lib().knc_prepare_ex(ptr, n, C.byref(opt), C.byref(self._h)))
+        self._keep = points if opt.points_on_device else None  # host input is not retained (kn_prepare)
+        self.info = self._info()
+
+    # -- reference interface -------------------------------------------------------------------------
+    def solve(self) -> "KnProblem":  # kn_solve, knearests.cu:348
+        _check(lib().knc_solve(self._h))
+        self.info = self._info()
+        return self
+
+    def get_points(self) -> np.ndarray:  # kn_get_points, knearests.cu:410
+        out = np.empty((self.info.n, 3), np.float32)
+        _check(lib().knc_get_points(self._h, out.ctypes.data))
+        return out
+
+    def get_permutation(self) -> np.ndarray:  # kn_get_permutation, knearests.cu:420
+        out = np.empty(self.info.n, np.uint32)
+        _check(lib().knc_get_permutation(self._h, out.ctypes.data))
+        return out
+
+    def get_knearests(self, out: np.ndarray | None = None) -> np.ndarray:  # kn_get_knearests, knearests.cu:430
+        if out is None:
+            out = np.empty((self.info.query_count, self.info.k), np.uint32)
+        _check(lib().knc_get_knearests(self._h, out.ctypes.data))
+        return out
+
+    def get_knearests_original(self) -> np.ndarray:  # the remap of test_knearests.cu:155-160
+        out = np.empty((self.info.n, self.info.k), np.uint32)
+        _check(lib().knc_get_knearests_original(self._h, out.ctypes.data))
+        return out
+
+    def stats(self) -> dict:  # kn_print_stats, knearests.cu:440
+        s = Stats()
+        _check(lib().knc_get_stats(self._h, C.byref(s)))
+        return {"cells": s.cells, "min": s.min_per_cell, "max": s.max_per_cell, "avg": s.avg_per_cell,
+                "total": s.total, "histogram": list(s.histogram)}
+
+    def free(self) -> None:  # kn_free, knearests.cu:396
+        if self._h:
+            lib().knc_free(self._h)
+            self._h = C.c_void_p()
+
+    # -- extras ----------------------------------------------------------------------------------------
+    def timings(self) -> dict:
+        t = Timings()
+        _check(lib().knc_get_timings(self._h, C.byref(t)))
+        return {"build_ms": t.build_ms, "solve_ms": t.solve_ms, "h2d_ms": t.h2d_ms, "restarts": t.restarts,
+                "max_radius2": t.max_radius2}
+
+    def _info(self) -> Info:
+        i = Info()
+        _check(lib().knc_get_info(self._h, C.byref(i)))
+        return i
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.free()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+# function-style mirror of knearests.h, for code that reads like the reference's test driver
+def kn_prepare(points, numpoints: int | None = None, k: int = 0) -> KnProblem:
+    pts = np.asarray(points, np.float32).reshape(-1, 3) if not hasattr(points, "is_cuda") else points
+    if numpoints is not None and not hasattr(points, "is_cuda"):
+        pts = pts[:numpoints]
+    return KnProblem(pts, k=k)
+
+
+def kn_solve(kn: KnProblem) -> None:
+    kn.solve()
+
+
+def kn_get_points(kn: KnProblem) -> np.ndarray:
+    return kn.get_points()
+
+
+def kn_get_knearests(kn: KnProblem) -> np.ndarray:
+    return kn.get_knearests()
+
+
+def kn_get_permutation(kn: KnProblem) -> np.ndarray:
+    return kn.get_permutation()
+
+
+def kn_print_stats(kn: KnProblem) -> None:
+    s = kn.stats()
+    print(f"Grid:  points per cell: {s['min']} (min), {s['max']} (max), {s['avg']:g} avg, total {s['total']}",
+          file=sys.stderr)
+    for c, v in enumerate(s["histogram"]):
+        if v:
+            print(f"[{c}] => {v}", file=sys.stderr)
+
+
+def kn_free(kn: KnProblem) -> None:
+    kn.free()
+
+
+def generate_uniform_device(n: int, seed: int = 20171004, first: int = 0, device=None):
+    """Synthetic uniform cloud of SURVEY 8d, generated on the GPU into a torch tensor [n,3]."""
+    import torch
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    with torch.cuda.device(dev):
+        t = torch.empty((n, 3), dtype=torch.float32, device=dev)
+        torch.cuda.current_stream().synchronize()
+        _check(lib().knc_generate_uniform_device(C.c_void_p(t.data_ptr()), first, n, seed))
+    return t

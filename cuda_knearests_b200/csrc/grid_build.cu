@@ -1,0 +1,351 @@
+// grid_build.cu -- uniform-grid construction for sm_100a: per-cell count, exclusive scan, stable
+// counting-sort scatter with the permutation.  Replaces the reference's count / reserve / store kernels
+// (knearests.cu:32-60) and their launcher kn_firstbuild (knearests.cu:152-201).
+//
+// What is different from the reference, and why:
+//  * count   : the histogram atomic also hands every point its arrival rank inside its cell, so the
+//              scatter needs no second round of atomics (the reference does 2 atomics per point,
+//              :36 and :56); atomics are warp-aggregated with match.any, which matters when the
+//              input arrives spatially coherent (many lanes of a warp in one cell).
+//  * reserve : a real exclusive prefix sum (single-pass, decoupled look-back) instead of
+//              atomicAdd(globalcounter, cnt) in arrival order (:45) => cells are laid out in ascending
+//              cell id, deterministic, and an x-row of cells is one contiguous span of points.
+//  * store   : ranks come from atomics, so the order inside a cell is arrival order; one extra pass
+//              sorts each cell's few entries by original index => the whole layout is the stable
+//              counting sort, bit-identical from run to run (the reference's is not).
+//  * the sorted points are written twice: float3 (the API's d_stored_points) and float4
+//              (x,y,z,bits(original index)) -- 16-byte records the query kernel loads with one LDG.128.
+//
+// HBM traffic per point (algorithmic): read 12 (count) + write 8 (cell id, rank) + read 8 / write 4
+// (scatter) + read 4+12 / write 12+16 (gather) + 8 per cell for the scan ~= 79 B/point.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "kn_internal.h"
+
+namespace {
+
+constexpr int kBuildThreads = 256;
+
+// cellFromPoint, one axis -- knearests.cu:23-28.  Must round exactly like the reference's PTX
+// (mul.f32, div.rn.f32, cvt.rmi, cvt.rzi): do NOT replace the division by a reciprocal multiply.
+__device__ __forceinline__ int axis_cell(float p, float Df, int lo, int hi) {
+    float t = floorf(__fdiv_rn(__fmul_rn(p, Df), 1000.f));
+    int c = (int)t;  // saturating, NaN -> 0
+    return max(lo, min(c, hi));
+}
+
+// ---------------------------------------------------------------------------------------- count
+// One point per thread; a block stages its 256 points (768 floats) through shared memory with
+// float4 loads, so global reads are 16-byte vectorised and fully coalesced although the input is AoS.
+__global__ void __launch_bounds__(kBuildThreads)
+kn_count_kernel(const float *__restrict__ xyz, int n, GridGeom g, int *__restrict__ counters,
+                int *__restrict__ cellid, int *__restrict__ rank, int aligned16) {
+    __shared__ __align__(16) float tile[kBuildThreads * 3];
+    const int tid = threadIdx.x;
+    const long long first = (long long)blockIdx.x * kBuildThreads;
+    const int here = (int)min((long long)kBuildThreads, (long long)n - first);
+    const float *src = xyz + first * 3;
+    if (aligned16 && here == kBuildThreads) {
+        if (tid < kBuildThreads * 3 / 4)
+            reinterpret_cast<float4 *>(tile)[tid] = __ldg(reinterpret_cast<const float4 *>(src) + tid);
+    } else {
+        for (int i = tid; i < here * 3; i += kBuildThreads) tile[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    const bool valid = tid < here;
+    int cell = -1 - (tid & 31);  // invalid lanes: unique keys, never grouped
+    if (valid) {
+        int i = axis_cell(tile[3 * tid], g.Df, 0, g.D - 1);
+        int j = axis_cell(tile[3 * tid + 1], g.Df, 0, g.D - 1);
+        int k = axis_cell(tile[3 * tid + 2], g.Df, g.zb, g.ze - 1) - g.zb;
+        cell = i + (j + k * g.D) * g.D;  // z-major, knearests.cu:29
+    }
+    // warp-aggregated atomic: lanes in the same cell elect a leader that adds the group size once
+    const unsigned peers = __match_any_sync(0xffffffffu, cell);
+    const int lane = tid & 31;
+    const int leader = __ffs(peers) - 1;
+    const int within = __popc(peers & ((1u << lane) - 1u));
+    int base = 0;
+    if (valid && lane == leader) base = atomicAdd(counters + cell, __popc(peers));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (valid) {
+        cellid[first + tid] = cell;
+        rank[first + tid] = base + within;
+    }
+}
+
+// ----------------------------------------------------------------------------------------- scan
+// Single-pass exclusive prefix sum with decoupled look-back.  Tile = 256 threads x 16 cells.
+// Tile state word: status in the top 2 bits (0 = not ready, 1 = tile aggregate, 2 = inclusive prefix),
+// value in the low 32 bits -- one 64-bit store publishes both, so no fence is needed between them.
+constexpr int kScanItems = 16;
+constexpr int kScanTile = kBuildThreads * kScanItems;
+
+__global__ void __launch_bounds__(kBuildThreads)
+kn_scan_kernel(const int *__restrict__ counters, int *__restrict__ ptrs, long long cells,
+               unsigned long long *tile_state, int *ticket, int *globcounter) {
+    __shared__ int s_tile;
+    __shared__ int s_warp[kBuildThreads / 32];
+    __shared__ int s_prefix;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_tile = atomicAdd(ticket, 1);  // tiles are numbered in the order blocks START
+    __syncthreads();
+    const int tile = s_tile;
+    const long long base = (long long)tile * kScanTile + (long long)tid * kScanItems;
+
+    int v[kScanItems];
+    if (base + kScanItems <= cells) {
+        const int4 *src = reinterpret_cast<const int4 *>(counters + base);
+#pragma unroll
+        for (int q = 0; q < kScanItems / 4; q++) {
+            int4 t = __ldg(src + q);
+            v[4 * q] = t.x; v[4 * q + 1] = t.y; v[4 * q + 2] = t.z; v[4 * q + 3] = t.w;
+        }
+    } else {
+#pragma unroll
+        for (int q = 0; q < kScanItems; q++) v[q] = (base + q < cells) ? __ldg(counters + base + q) : 0;
+    }
+    int sum = 0;
+#pragma unroll
+    for (int q = 0; q < kScanItems; q++) sum += v[q];
+    int incl = sum;  // inclusive scan of the per-thread sums across the warp
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    int warp_off = 0, tile_sum = 0;
+#pragma unroll
+    for (int wq = 0; wq < kBuildThreads / 32; wq++) {
+        int t = s_warp[wq];
+        if (wq < warp) warp_off += t;
+        tile_sum += t;
+    }
+    const int thread_excl = warp_off + incl - sum;
+
+    if (warp == 0) {
+        volatile unsigned long long *st = tile_state;
+        if (lane == 0)
+            st[tile] = ((unsigned long long)(tile == 0 ? 2 : 1) << 62) | (unsigned)tile_sum;
+        int exclusive = 0;
+        if (tile > 0) {
+            int look = tile - 1;  // lane L inspects tile look - L
+            while (true) {
+                unsigned long long wrd = 0;
+                const int idx = look - lane;
+                if (idx >= 0) {
+                    do { wrd = st[idx]; } while ((wrd >> 62) == 0);
+                } else {
+                    wrd = 2ull << 62;  // before tile 0: inclusive prefix 0
+                }
+                const unsigned full = __ballot_sync(0xffffffffu, (wrd >> 62) == 2);
+                const int stop = full ? __ffs(full) - 1 : 32;  // nearest tile with an inclusive prefix
+                int contrib = (lane <= stop) ? (int)(unsigned)wrd : 0;
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, d);
+                exclusive += contrib;
+                if (full) break;
+                look -= 32;
+            }
+            if (lane == 0) st[tile] = (2ull << 62) | (unsigned)(exclusive + tile_sum);
+        }
+        if (lane == 0) s_prefix = exclusive;
+    }
+    __syncthreads();
+    int run = s_prefix + thread_excl;
+    if (base + kScanItems <= cells) {
+        int4 *dst = reinterpret_cast<int4 *>(ptrs + base);
+#pragma unroll
+        for (int q = 0; q < kScanItems / 4; q++) {
+            int4 t;
+            t.x = run; run += v[4 * q];
+            t.y = run; run += v[4 * q + 1];
+            t.z = run; run += v[4 * q + 2];
+            t.w = run; run += v[4 * q + 3];
+            dst[q] = t;
+        }
+    } else {
+#pragma unroll
+        for (int q = 0; q < kScanItems; q++) {
+            if (base + q < cells) ptrs[base + q] = run;
+            run += v[q];
+        }
+    }
+    // the tile that covers the last cell also writes the total (ptrs[cells]) and the public counter
+    if ((long long)(tile + 1) * kScanTile >= cells && tid == kBuildThreads - 1) {
+        ptrs[cells] = s_prefix + tile_sum;
+        *globcounter = s_prefix + tile_sum;
+    }
+}
+
+// -------------------------------------------------------------------------------------- scatter
+__global__ void __launch_bounds__(kBuildThreads)
+kn_scatter_kernel(int n, const int *__restrict__ cellid, const int *__restrict__ rank,
+                  const int *__restrict__ ptrs, unsigned int *__restrict__ permutation) {
+    const long long i = (long long)blockIdx.x * kBuildThreads + threadIdx.x;
+    if (i < n) permutation[__ldg(ptrs + __ldg(cellid + i)) + __ldg(rank + i)] = (unsigned)i;
+}
+
+// ---------------------------------------------------------------------------------------- order
+// Puts each cell's slice of the permutation into ascending original index.  One thread per cell:
+// up to 8 entries go through a fixed 19-comparator network in registers, up to KN_BIG_CELL through an
+// in-place insertion sort, larger cells are queued for kn_order_big_kernel.
+__device__ __forceinline__ void cmpswap(unsigned &a, unsigned &b) {
+    const unsigned lo = min(a, b), hi = max(a, b);
+    a = lo; b = hi;
+}
+
+__global__ void __launch_bounds__(kBuildThreads)
+kn_order_kernel(long long cells, const int *__restrict__ ptrs, unsigned int *__restrict__ permutation,
+                int *big_count, int *__restrict__ big_list) {
+    const long long c = (long long)blockIdx.x * kBuildThreads + threadIdx.x;
+    if (c >= cells) return;
+    const int b = __ldg(ptrs + c), cnt = __ldg(ptrs + c + 1) - b;
+    if (cnt < 2) return;
+    unsigned *seg = permutation + b;
+    if (cnt <= 8) {
+        unsigned v[8];
+#pragma unroll
+        for (int q = 0; q < 8; q++) v[q] = q < cnt ? seg[q] : 0xFFFFFFFFu;
+        cmpswap(v[0], v[1]); cmpswap(v[2], v[3]); cmpswap(v[4], v[5]); cmpswap(v[6], v[7]);
+        cmpswap(v[0], v[2]); cmpswap(v[1], v[3]); cmpswap(v[4], v[6]); cmpswap(v[5], v[7]);
+        cmpswap(v[1], v[2]); cmpswap(v[5], v[6]); cmpswap(v[0], v[4]); cmpswap(v[3], v[7]);
+        cmpswap(v[1], v[5]); cmpswap(v[2], v[6]);
+        cmpswap(v[1], v[4]); cmpswap(v[3], v[6]);
+        cmpswap(v[2], v[4]); cmpswap(v[3], v[5]);
+        cmpswap(v[3], v[4]);
+#pragma unroll
+        for (int q = 0; q < 8; q++)
+            if (q < cnt) seg[q] = v[q];
+    } else if (cnt <= KN_BIG_CELL) {
+        for (int a = 1; a < cnt; a++) {
+            const unsigned key = seg[a];
+            int s = a;
+            while (s > 0 && seg[s - 1] > key) { seg[s] = seg[s - 1]; s--; }
+            seg[s] = key;
+        }
+    } else {
+        big_list[atomicAdd(big_count, 1)] = (int)c;
+    }
+}
+
+// One block per oversized cell: bitonic network, every compare-exchange ascending (partner = mirror in
+// the first step of a merge, i ^ j afterwards), so the virtual +inf padding beyond `cnt` never moves.
+__global__ void __launch_bounds__(1024)
+kn_order_big_kernel(const int *big_count, const int *__restrict__ big_list, const int *__restrict__ ptrs,
+                    unsigned int *__restrict__ permutation) {
+    const int nbig = *big_count;
+    for (int w = blockIdx.x; w < nbig; w += gridDim.x) {
+        const int c = big_list[w];
+        const int b = ptrs[c];
+        const unsigned cnt = (unsigned)(ptrs[c + 1] - b);
+        unsigned *seg = permutation + b;
+        for (unsigned long long k = 2; (k >> 1) < cnt; k <<= 1) {
+            for (unsigned long long j = k >> 1; j > 0; j >>= 1) {
+                for (unsigned long long t = threadIdx.x; t < cnt; t += blockDim.x) {
+                    const unsigned long long partner = (j == (k >> 1)) ? (t ^ (k - 1)) : (t ^ j);
+                    if (partner > t && partner < cnt) {
+                        const unsigned a = seg[t], d = seg[partner];
+                        if (a > d) { seg[t] = d; seg[partner] = a; }
+                    }
+                }
+                __syncthreads();
+            }
+        }
+    }
+}
+
+// --------------------------------------------------------------------------------------- gather
+__global__ void __launch_bounds__(kBuildThreads)
+kn_gather_kernel(const float *__restrict__ xyz, int n, const unsigned int *__restrict__ permutation,
+                 float *__restrict__ points3, float4 *__restrict__ points4) {
+    __shared__ float tile[kBuildThreads * 3];
+    const int tid = threadIdx.x;
+    const long long first = (long long)blockIdx.x * kBuildThreads;
+    const long long s = first + tid;
+    const int here = (int)min((long long)kBuildThreads, (long long)n - first);
+    if (s < n) {
+        const unsigned i = __ldg(permutation + s);
+        const float x = __ldg(xyz + 3ll * i), y = __ldg(xyz + 3ll * i + 1), z = __ldg(xyz + 3ll * i + 2);
+        points4[s] = make_float4(x, y, z, __uint_as_float(i));
+        tile[3 * tid] = x; tile[3 * tid + 1] = y; tile[3 * tid + 2] = z;
+    }
+    __syncthreads();
+    // AoS float3 output written as one contiguous, coalesced run per block
+    float *dst = points3 + first * 3;
+    for (int q = tid; q < here * 3; q += kBuildThreads) dst[q] = tile[q];
+}
+
+// ------------------------------------------------------------------------------ synthetic input
+__device__ __forceinline__ unsigned long long splitmix64(unsigned long long x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+__global__ void kn_generate_kernel(float *xyz, long long first, long long count3, unsigned long long seed) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count3) return;
+    const unsigned long long u = splitmix64(seed ^ (unsigned long long)(3 * first + t));
+    xyz[t] = __fmul_rn(1000.0f, __fmul_rn((float)(u >> 40), 1.0f / 16777216.0f));
+}
+
+// out[perm[s]*k + j] = perm[knn[s*k + j]]  (test_knearests.cu:155-160 on the device)
+__global__ void kn_remap_original_kernel(const unsigned int *__restrict__ knn,
+                                         const unsigned int *__restrict__ perm, long long total, int k,
+                                         unsigned int *__restrict__ out) {
+    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= total) return;
+    const long long s = e / k;
+    const int j = (int)(e - s * k);
+    const unsigned v = __ldg(knn + e);
+    out[(long long)__ldg(perm + s) * k + j] = (v == KNC_EMPTY) ? KNC_EMPTY : __ldg(perm + v);
+}
+
+inline unsigned blocks_for(long long items, int per_block) {
+    return (unsigned)((items + per_block - 1) / per_block);
+}
+
+}  // namespace
+
+size_t kn_build_scratch_tiles(long long cells) { return (size_t)((cells + kScanTile - 1) / kScanTile); }
+
+cudaError_t kn_launch_build(const float *d_in_xyz, int n, const GridGeom &g, long long cells, int *d_counters,
+                            int *d_ptrs, int *d_globcounter, unsigned int *d_permutation, float *d_points3,
+                            float4 *d_points4, const BuildScratch &s, cudaStream_t st) {
+    cudaError_t e;
+    if ((e = cudaMemsetAsync(d_counters, 0, sizeof(int) * (size_t)cells, st)) != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(s.d_tile, 0, sizeof(unsigned long long) * s.tile_count, st)) != cudaSuccess) return e;
+    if ((e = cudaMemsetAsync(s.d_ticket, 0, sizeof(int) * 2, st)) != cudaSuccess) return e;
+    const int aligned16 = ((uintptr_t)d_in_xyz & 15u) == 0;
+    kn_count_kernel<<<blocks_for(n, kBuildThreads), kBuildThreads, 0, st>>>(d_in_xyz, n, g, d_counters,
+                                                                           s.d_cellid, s.d_rank, aligned16);
+    kn_scan_kernel<<<(unsigned)s.tile_count, kBuildThreads, 0, st>>>(d_counters, d_ptrs, cells, s.d_tile,
+                                                                    s.d_ticket, d_globcounter);
+    kn_scatter_kernel<<<blocks_for(n, kBuildThreads), kBuildThreads, 0, st>>>(n, s.d_cellid, s.d_rank, d_ptrs,
+                                                                             d_permutation);
+    kn_order_kernel<<<blocks_for(cells, kBuildThreads), kBuildThreads, 0, st>>>(cells, d_ptrs, d_permutation,
+                                                                               s.d_ticket + 1, s.d_biglist);
+    kn_order_big_kernel<<<148, 1024, 0, st>>>(s.d_ticket + 1, s.d_biglist, d_ptrs, d_permutation);
+    kn_gather_kernel<<<blocks_for(n, kBuildThreads), kBuildThreads, 0, st>>>(d_in_xyz, n, d_permutation,
+                                                                            d_points3, d_points4);
+    return cudaGetLastError();
+}
+
+cudaError_t kn_launch_generate(float *d_xyz, long long first, long long count, uint64_t seed, cudaStream_t st) {
+    const long long count3 = count * 3;
+    if (count3 > 0)
+        kn_generate_kernel<<<blocks_for(count3, 256), 256, 0, st>>>(d_xyz, first, count3, seed);
+    return cudaGetLastError();
+}
+
+cudaError_t kn_launch_remap_original(const unsigned int *d_knn, const unsigned int *d_perm, int n, int k,
+                                     unsigned int *d_out, cudaStream_t st) {
+    const long long total = (long long)n * k;
+    if (total > 0)
+        kn_remap_original_kernel<<<blocks_for(total, 256), 256, 0, st>>>(d_knn, d_perm, total, k, d_out);
+    return cudaGetLastError();
+}

@@ -1,0 +1,61 @@
+// kn_internal.h -- private state and launcher prototypes of libknearests_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "knearests.h"
+#include "knearests_c.h"
+
+// The handle.  Its first member is the reference-compatible public struct (knearests.h), so a
+// kn_problem* handed to reference-style callers and a knc_problem* are the same address.
+struct knc_problem {
+    kn_problem pub;
+    int k;
+    int device;
+    float density;
+    float search_scale;
+    int z_begin, z_end;          // cell planes held (z_end - z_begin == pub.dimz planes LOCALLY)
+    int own_z_begin, own_z_end;
+    int dim_global;              // global cubic resolution D (pub.dimx == pub.dimy == D)
+    long long cells;             // D * D * (z_end - z_begin)
+    int query_begin, query_count;
+    int solved;
+    float4 *d_points4;           // [n] x, y, z, bits(original index): what the query kernel reads
+    unsigned int *d_diag;        // [4] restarts, max radius^2 bits, halo misses, spare
+    cudaStream_t stream;
+    cudaEvent_t ev[4];
+    knc_timings t;
+};
+
+// Grid geometry handed to kernels.
+struct GridGeom {
+    int D;          // global resolution in x and y (and z, globally)
+    int zb, ze;     // cell planes held locally: [zb, ze)
+    float Df;       // (float)D
+    float w;        // cell width 1000 / D
+    float invw;     // D / 1000
+};
+
+// ---- grid_build.cu -----------------------------------------------------------------------------
+struct BuildScratch {
+    int *d_cellid;               // [n]
+    int *d_rank;                 // [n]
+    unsigned long long *d_tile;  // scan tile states
+    int *d_ticket;               // scan ticket + big-cell worklist counter
+    int *d_biglist;              // [n / KN_BIG_CELL + 1] cells too large for the per-thread ordering
+    size_t tile_count;
+};
+size_t kn_build_scratch_tiles(long long cells);
+cudaError_t kn_launch_build(const float *d_in_xyz, int n, const GridGeom &g, long long cells, int *d_counters,
+                            int *d_ptrs, int *d_globcounter, unsigned int *d_permutation, float *d_points3,
+                            float4 *d_points4, const BuildScratch &s, cudaStream_t st);
+cudaError_t kn_launch_generate(float *d_xyz, long long first, long long count, uint64_t seed, cudaStream_t st);
+cudaError_t kn_launch_remap_original(const unsigned int *d_knn, const unsigned int *d_perm, int n, int k,
+                                     unsigned int *d_out, cudaStream_t st);
+
+// ---- knn_query.cu ------------------------------------------------------------------------------
+cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const GridGeom &g, int n, int k,
+                            int query_begin, int query_count, float radius0_sq, unsigned int *d_knn,
+                            unsigned int *d_diag, cudaStream_t st);
+
+#define KN_BIG_CELL 32  // cells with more points than this are ordered by a whole block, not a thread

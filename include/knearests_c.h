@@ -1,0 +1,149 @@
+/* knearests_c.h -- the C ABI of the B200 kNN engine (libknearests_b200.so).
+ *
+ * Plain pointers and sizes, status codes instead of exit(), no C++ or torch types: this is what an FFI
+ * (ctypes, cgo, JNI, dlopen) binds.  Every entry point names the reference interface it replaces
+ * (file:line in ssloy/cuda_knearests).  The reference's own header has no extern "C" (SURVEY F4); its
+ * seven C++-linkage functions are kept, as wrappers over these, in knearests.h.
+ *
+ * Model: one handle = one point cloud on one GPU (the current device at prepare time).  A handle is
+ * not thread-safe; distinct handles are independent.  All calls are synchronous: when they return,
+ * the device work they describe is complete (as in the reference, knearests.cu:196,373).
+ *
+ * Index spaces (knearests.cu:57, test_knearests.cu:158):
+ *   original index  i : position of a point in the caller's input array
+ *   sorted position s : position in cell order; permutation[s] = i
+ * Cell order is deterministic: ascending cell id (x fastest, z slowest, knearests.cu:29), and inside a
+ * cell ascending original index.  A neighbour row is ascending in the total order
+ * (squared distance, sorted position), where the squared distance is the reference's f32 expression
+ * fma(dz,dz, fma(dx,dx, dy*dy)) (knearests.cu:125 as nvcc contracts it).  The point itself is excluded
+ * by position, coincident points are not (knearests.cu:123).
+ */
+#ifndef KNEARESTS_B200_C_H
+#define KNEARESTS_B200_C_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- status codes ------------------------------------------------------------------------------- */
+#define KNC_OK 0
+#define KNC_ERR_INVALID 1     /* bad argument (null pointer, n < 1, k out of range, bad slab)       */
+#define KNC_ERR_CUDA 2        /* a CUDA runtime call failed; knc_last_error() has the CUDA string   */
+#define KNC_ERR_NOMEM 3       /* host or device allocation failed                                   */
+#define KNC_ERR_STATE 4       /* call order: results requested before knc_solve                     */
+#define KNC_ERR_HALO 5        /* slab mode: some query needed points beyond the halo it was given   */
+
+#define KNC_EMPTY 0xFFFFFFFFu /* row entry meaning "no such neighbour" (UINT_MAX, knearests.cu:108) */
+#define KNC_MAX_K 256         /* largest supported k                                                */
+
+typedef struct knc_problem knc_problem; /* opaque; its first bytes are a kn_problem (knearests.h) */
+
+/* Options for knc_prepare_ex.  Zero-initialise, set struct_size = sizeof(knc_options), then set
+ * what you need; a zero field means "default". */
+typedef struct {
+    size_t struct_size;
+    int k;                  /* neighbours per point; default = library's DEFAULT_NB_PLANES (params.h:4) */
+    float density;          /* target points per grid cell; default 3.1f (knearests.cu:249)             */
+    int points_on_device;   /* 1: `xyz` is a DEVICE pointer on the current device (no H2D copy)         */
+    int grid_dim;           /* force the cubic grid resolution D (default: from n and density)          */
+    /* z-slab mode (multi-GPU): the handle holds only cell planes [z_begin, z_end) of a
+     * global D^3 grid (grid_dim must be set) and answers queries only for the points in planes
+     * [own_z_begin, own_z_end); the other planes are a read-only halo.  All zero = whole grid. */
+    int z_begin, z_end;
+    int own_z_begin, own_z_end;
+    float search_scale;     /* tuning: multiplies the first-guess search radius; default 1             */
+} knc_options;
+
+/* What the handle holds; device pointers are valid until knc_free. */
+typedef struct {
+    int n;                  /* points held (slab mode: owned + halo)                                    */
+    int k;
+    int dimx, dimy, dimz;   /* GLOBAL grid resolution                                                   */
+    int z_begin, z_end;     /* cell planes held                                                         */
+    int query_begin;        /* first sorted position that is a query                                    */
+    int query_count;        /* number of queries = rows of d_knearests                                  */
+    int solved;             /* 1 after knc_solve                                                        */
+    const float *d_points;          /* [n*3]  sorted points, AoS xyz (kn_problem.d_stored_points)       */
+    const float *d_points4;         /* [n*4]  sorted points as x,y,z,bits(original index)               */
+    const unsigned int *d_permutation; /* [n]                                                           */
+    const int *d_counters;          /* [cells]                                                          */
+    const int *d_ptrs;              /* [cells + 1]                                                      */
+    const unsigned int *d_knearests;   /* [query_count * k], row r = query sorted position query_begin+r */
+} knc_info;
+
+/* Grid occupancy, the numbers kn_print_stats prints (knearests.cu:440-466). */
+typedef struct {
+    long long cells;
+    int min_per_cell, max_per_cell;
+    double avg_per_cell;
+    long long total;            /* sum of the counters = n                                              */
+    long long histogram[64];    /* histogram[c] = cells holding c points; the last bin also counts more */
+} knc_stats;
+
+/* Device time of the last prepare / solve on this handle, in milliseconds (CUDA events; what the
+ * reference prints as "kn_firstbuild: X msec" / "kn_solve: X msec", knearests.cu:200,376). */
+typedef struct {
+    float build_ms;         /* grid build kernels only (count, scan, scatter, order, gather)            */
+    float solve_ms;         /* query kernel only                                                        */
+    float h2d_ms;           /* host->device copy of the input inside knc_prepare (0 for device input)   */
+    unsigned int restarts;  /* queries whose first-guess radius was too small (diagnostic)              */
+    float max_radius2;      /* largest squared search radius any query ended with                       */
+} knc_timings;
+
+/* ---- the hot path -------------------------------------------------------------------------------- */
+
+/* Replaces kn_prepare (knearests.h:21, knearests.cu:235-344): copy n HOST points (AoS xyz f32) to the
+ * device, build the grid.  k <= 0 selects the default.  On success *out is a new handle. */
+int knc_prepare(const float *xyz, int n, int k, knc_problem **out);
+
+/* Same with options: device-resident input, grid density, forced resolution, z-slab mode. */
+int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem **out);
+
+/* Replaces kn_solve (knearests.h:22, knearests.cu:348-392): the all-points kNN query.  Blocking.
+ * May be called again; it recomputes the same rows. */
+int knc_solve(knc_problem *p);
+
+/* Replaces kn_free (knearests.h:23, knearests.cu:396-408).  NULL is accepted. */
+int knc_free(knc_problem *p);
+
+/* Replace kn_get_points / kn_get_permutation / kn_get_knearests (knearests.h:25-27,
+ * knearests.cu:410-438), writing into CALLER-provided host buffers instead of malloc()ing:
+ *   out_xyz   3*n floats            out_perm  n unsigned          out_knn  query_count*k unsigned  */
+int knc_get_points(knc_problem *p, float *out_xyz);
+int knc_get_permutation(knc_problem *p, unsigned int *out_perm);
+int knc_get_knearests(knc_problem *p, unsigned int *out_knn);
+
+/* The same rows in ORIGINAL index space -- the remap every caller of the reference does on the CPU
+ * (test_knearests.cu:155-160), done on the device: out[perm[s]*k + j] = perm[knn[s*k + j]].
+ * Whole-grid handles only (not slab mode).  out: n*k unsigned, host. */
+int knc_get_knearests_original(knc_problem *p, unsigned int *out_neighbors);
+
+/* Replaces kn_print_stats (knearests.h:29, knearests.cu:440-466), as data. */
+int knc_get_stats(knc_problem *p, knc_stats *out);
+
+/* ---- introspection ------------------------------------------------------------------------------- */
+int knc_get_info(knc_problem *p, knc_info *out);
+int knc_get_timings(knc_problem *p, knc_timings *out);
+
+/* Grid resolution the engine would choose: max(1, round(cbrt(n / density))) (knearests.cu:249). */
+int knc_grid_dim(int n, float density);
+
+/* Message of the last failure on the calling thread ("" if none). */
+const char *knc_last_error(void);
+
+/* Library build information: "knearests_b200 <version> sm_100a k_default=<K>". */
+const char *knc_version(void);
+
+/* ---- synthetic input (bench / tests) --------------------------------------------------
+ * Fills d_xyz (DEVICE, 3*count floats) with points [first, first+count) of the counter-based uniform
+ * cloud: u = splitmix64(seed ^ (3*i + c)), coord = 1000 * (u >> 40) * 2^-24.  No reference counterpart
+ * (the reference has no generator); bit-identical to oracle/knn_oracle.c:kno_generate_uniform. */
+int knc_generate_uniform_device(float *d_xyz, long long first, long long count, uint64_t seed);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KNEARESTS_B200_C_H */

@@ -1,0 +1,253 @@
+"""GPU parity: the CUDA engine, called through its C ABI, against the oracle -- bit exact.
+
+Grid build (layout, permutation) and neighbour rows are integer/index work: every comparison here is
+array equality, no tolerance.  The engine's rows are defined by the total order
+(d2, sorted position) with d2 = fma(dz,dz,fma(dx,dx,dy*dy)) (knearests.cu:125 as compiled), which
+oracle.Grid.knn_exact computes independently on the CPU.
+"""
+import numpy as np
+import pytest
+
+from conftest import GOLDEN, assert_sets_match_golden_hash, set_hash
+
+pytestmark = pytest.mark.gpu
+
+
+def run_engine(kn, pts, K, **kw):
+    with kn.KnProblem(pts, k=K, **kw) as p:
+        p.solve()
+        return {"knn": p.get_knearests(), "perm": p.get_permutation(), "points": p.get_points(),
+                "stats": p.stats(), "dim": p.info.dimx, "timings": p.timings(), "info": p.info}
+
+
+def assert_layout_equals_oracle(oracle, pts, res, **gridkw):
+    g = oracle.Grid(pts, **gridkw)
+    assert res["dim"] == g.dim
+    assert np.array_equal(res["perm"], g.permutation)          # stable counting sort, knearests.cu:51-60
+    assert np.array_equal(res["points"], g.sorted_xyz)
+    hist = np.bincount(g.counters, minlength=64)
+    assert res["stats"]["histogram"][:63] == hist[:63].tolist()  # what kn_print_stats prints
+    assert res["stats"]["total"] == pts.shape[0]
+    return g
+
+
+@pytest.mark.parametrize("K", [1, 8, 13, 20, 32, 50, 100, 200, 256])
+def test_pts20k_rows_bit_exact(kn, oracle, pts20k, K):
+    res = run_engine(kn, pts20k, K)
+    g = assert_layout_equals_oracle(oracle, pts20k, res)
+    assert np.array_equal(res["knn"], g.knn_exact(K))
+
+
+@pytest.mark.parametrize("K", [8, 20, 50])
+def test_pts20k_sets_match_reference_kdtree_golden(kn, oracle, pts20k, K):
+    """The reference's own acceptance test (test_knearests.cu:194-232): set equality with kd_tree.cpp."""
+    res = run_engine(kn, pts20k, K)
+    idx, _ = oracle.canonical_rows(res["knn"], res["perm"], pts20k)
+    golden = np.load(GOLDEN / f"pts20k_kdtree_k{K}_rowhash.npy")
+    mism = np.nonzero(set_hash(idx) != golden)[0]
+    # the only rows that may differ are the fixture's exact k/k+1 ties, checked row by row on the oracle
+    g = oracle.Grid(pts20k)
+    assert np.array_equal(res["knn"], g.knn_exact(K))
+    assert len(mism) == assert_sets_match_golden_hash(oracle, pts20k, g, K, golden)
+
+
+@pytest.mark.parametrize("n,K,seed", [(11545, 50, 1), (100_000, 20, 2), (300_000, 50, 20171004),
+                                      (1_000_000, 20, 20171004), (1_000_000, 8, 1), (500_000, 32, 2)])
+def test_uniform_rows_bit_exact(kn, oracle, n, K, seed):
+    pts = oracle.generate_uniform(n, seed=seed)
+    res = run_engine(kn, pts, K)
+    g = assert_layout_equals_oracle(oracle, pts, res)
+    assert np.array_equal(res["knn"], g.knn_exact(K))
+    assert res["timings"]["restarts"] < n // 20
+
+
+@pytest.mark.parametrize("density", [0.5, 1.0, 2.0, 8.0])
+def test_other_grid_densities(kn, oracle, density):
+    pts = oracle.generate_uniform(200_000, seed=5)
+    res = run_engine(kn, pts, 20, density=density)
+    g = assert_layout_equals_oracle(oracle, pts, res, density=density)
+    assert np.array_equal(res["knn"], g.knn_exact(20))
+
+
+def test_device_input_equals_host_input(kn, oracle):
+    import torch
+    n = 250_000
+    dev = kn.generate_uniform_device(n, seed=20171004)
+    host = oracle.generate_uniform(n, seed=20171004)
+    assert np.array_equal(dev.cpu().numpy(), host)  # device generator == oracle generator, bit for bit
+    a = run_engine(kn, host, 20)
+    b = run_engine(kn, dev, 20)
+    for key in ("knn", "perm", "points"):
+        assert np.array_equal(a[key], b[key])
+    # unaligned device pointer takes the scalar load path of the count kernel
+    shifted = torch.empty(3 * n + 1, dtype=torch.float32, device="cuda")[1:].view(n, 3)
+    shifted.copy_(dev)
+    c = run_engine(kn, shifted, 20)
+    assert np.array_equal(a["knn"], c["knn"]) and np.array_equal(a["perm"], c["perm"])
+
+
+def test_solve_is_idempotent_and_deterministic(kn, oracle):
+    pts = oracle.generate_uniform(150_000, seed=11)
+    with kn.KnProblem(pts, k=20) as p:
+        a = p.solve().get_knearests()
+        b = p.solve().get_knearests()  # kn_solve may be called twice
+    c = run_engine(kn, pts, 20)["knn"]
+    assert np.array_equal(a, b) and np.array_equal(a, c)
+
+
+def test_original_space_remap(kn, oracle):
+    pts = oracle.generate_uniform(60_000, seed=4)
+    with kn.KnProblem(pts, k=8) as p:
+        p.solve()
+        knn, perm, orig = p.get_knearests(), p.get_permutation(), p.get_knearests_original()
+    want = np.empty_like(orig)
+    want[perm] = perm[knn]  # test_knearests.cu:155-160
+    assert np.array_equal(orig, want)
+    # the reference's checks: permutation is a bijection (:162-168), no duplicate in a row (:174-191)
+    assert np.array_equal(np.sort(perm), np.arange(len(perm), dtype=np.uint32))
+    srt = np.sort(orig, axis=1)
+    assert (np.diff(srt.astype(np.int64), axis=1) > 0).all()
+
+
+# ------------------------------------------------------------------------------------ edge cases
+def test_single_point_and_fewer_points_than_k(kn, oracle):
+    one = np.array([[500.0, 500.0, 500.0]], np.float32)
+    r = run_engine(kn, one, 8)
+    assert r["knn"].shape == (1, 8) and (r["knn"] == kn.EMPTY).all()
+    pts = oracle.generate_uniform(7, seed=3)
+    r = run_engine(kn, pts, 20)
+    g = oracle.Grid(pts)
+    assert np.array_equal(r["knn"], g.knn_exact(20))
+    assert (r["knn"][:, 6:] == kn.EMPTY).all() and (r["knn"][:, :6] != kn.EMPTY).all()
+
+
+def test_small_clouds_below_reference_minimum(kn, oracle):
+    # the reference exits below D = 16 (knearests.cu:255-258); the engine accepts any n >= 1
+    for n in (2, 33, 500, 5000):
+        pts = oracle.generate_uniform(n, seed=n)
+        r = run_engine(kn, pts, 8)
+        g = assert_layout_equals_oracle(oracle, pts, r)
+        assert np.array_equal(r["knn"], g.knn_exact(8))
+
+
+def test_coincident_points(kn, oracle):
+    # duplicates are neighbours of each other at distance 0; only the point itself is excluded (:123)
+    base = oracle.generate_uniform(20_000, seed=8)
+    pts = np.concatenate([base, base[:5000], base[:100], base[:100]])
+    r = run_engine(kn, pts, 8)
+    g = assert_layout_equals_oracle(oracle, pts, r)
+    assert np.array_equal(r["knn"], g.knn_exact(8))
+
+
+def test_points_outside_the_unit_range_are_clamped(kn, oracle):
+    # knearests.cu:21-30: out-of-range points land in border cells; still found, still exact
+    pts = oracle.generate_uniform(30_000, seed=6)
+    pts[:300] = pts[:300] * 1.2 - 100.0
+    pts[300:320] = [-50.0, 1050.0, 500.0]
+    r = run_engine(kn, pts, 20)
+    g = assert_layout_equals_oracle(oracle, pts, r)
+    assert np.array_equal(r["knn"], g.knn_exact(20))
+
+
+def test_clustered_cloud_overfull_cells_and_restarts(kn, oracle):
+    # far from uniform: most of the cloud in two tiny blobs (cells with thousands of points -> the
+    # block-wide ordering path of the build), the rest sparse (radius guess far too small -> restarts)
+    rng = np.random.default_rng(5)
+    blob1 = (rng.normal(0, 0.4, (6000, 3)) + [200, 300, 400]).astype(np.float32)
+    blob2 = (rng.normal(0, 2.0, (3000, 3)) + [800, 800, 100]).astype(np.float32)
+    sparse = oracle.generate_uniform(3000, seed=12)
+    pts = np.ascontiguousarray(np.concatenate([blob1, sparse, blob2])[rng.permutation(12000)])
+    r = run_engine(kn, pts, 20)
+    g = assert_layout_equals_oracle(oracle, pts, r)
+    assert r["stats"]["max"] > 1000
+    assert np.array_equal(r["knn"], g.knn_exact(20))
+    assert r["timings"]["restarts"] > 0
+
+
+def test_planar_and_lattice_clouds_with_many_ties(kn, oracle):
+    # integer lattice: massive distance ties, including at the k/k+1 border -> the stated tie-break
+    ax = np.arange(0, 40, dtype=np.float32) * 25.0 + 12.5
+    lattice = np.stack(np.meshgrid(ax, ax, ax, indexing="ij"), -1).reshape(-1, 3)
+    r = run_engine(kn, lattice, 20)
+    g = assert_layout_equals_oracle(oracle, lattice, r)
+    assert np.array_equal(r["knn"], g.knn_exact(20))
+    plane = oracle.generate_uniform(40_000, seed=2)
+    plane[:, 2] = 500.0
+    r = run_engine(kn, plane, 8)
+    g = assert_layout_equals_oracle(oracle, plane, r)
+    assert np.array_equal(r["knn"], g.knn_exact(8))
+
+
+def test_slab_mode_rows_equal_whole_grid_rows(kn, oracle):
+    """z-slab handles: planes [zb,ze) held, queries for [ozb,oze) only; the rows are the
+    whole-grid rows, shifted by the slab's first sorted position."""
+    pts = oracle.generate_uniform(400_000, seed=20171004)
+    K = 20
+    g = oracle.Grid(pts)
+    D = g.dim
+    full = g.knn_exact(K)
+    cz = np.clip(np.floor(pts[:, 2] * np.float32(D) / np.float32(1000)).astype(int), 0, D - 1)
+    for (zb, ze, ozb, oze) in [(0, 14, 0, 10), (6, 30, 10, 26), (D - 16, D, D - 12, D)]:
+        keep = (cz >= zb) & (cz < ze)
+        sub = np.ascontiguousarray(pts[keep])
+        with kn.KnProblem(sub, k=K, grid_dim=D, slab=(zb, ze, ozb, oze)) as p:
+            p.solve()
+            rows, perm, info = p.get_knearests(), p.get_permutation(), p.info
+        # global sorted positions of the slab: contiguous, starting at ptrs[zb * D * D]
+        base = int(g.ptrs[zb * D * D])
+        q0 = int(g.ptrs[ozb * D * D]) - base
+        q1 = int(g.ptrs[oze * D * D]) - base
+        assert (info.query_begin, info.query_count) == (q0, q1 - q0)
+        want = full[base + q0: base + q1].astype(np.int64) - base
+        assert np.array_equal(rows.astype(np.int64), want)
+        assert np.array_equal(np.nonzero(keep)[0][perm], g.permutation[base: base + sub.shape[0]])
+
+
+def test_slab_mode_reports_insufficient_halo(kn, oracle):
+    pts = oracle.generate_uniform(100_000, seed=3)
+    D = oracle.grid_dim(len(pts))
+    cz = np.clip(np.floor(pts[:, 2] * np.float32(D) / np.float32(1000)).astype(int), 0, D - 1)
+    sub = np.ascontiguousarray(pts[(cz >= 10) & (cz < 20)])
+    with kn.KnProblem(sub, k=20, grid_dim=D, slab=(10, 20, 10, 20)) as p:  # no halo at all
+        with pytest.raises(kn.KnError) as e:
+            p.solve()
+        assert e.value.code == 5  # KNC_ERR_HALO
+
+
+# ------------------------------------------------------------------------ BASELINE sizes: properties
+def test_ten_million_points_properties_and_sampled_brute_force(kn, oracle):
+    """configs[2]: 10 M uniform, k = 20.  Too big for the O(n) oracle per query on all rows, so:
+    size-independent properties on everything + exact brute force on sampled queries."""
+    import torch
+    n, K = 10_000_000, 20
+    dev = kn.generate_uniform_device(n, seed=20171004)
+    with kn.KnProblem(dev, k=K) as p:
+        p.solve()
+        knn = p.get_knearests()
+        perm = p.get_permutation()
+        pts = p.get_points()
+        assert p.info.dimx == 148
+    # permutation is a bijection (test_knearests.cu:162-168)
+    seen = np.zeros(n, np.uint8)
+    seen[perm] = 1
+    assert seen.all()
+    host = dev.cpu().numpy()
+    assert np.array_equal(pts[:100000], host[perm[:100000]])
+    assert (knn != kn.EMPTY).all() and (knn != np.arange(n, dtype=np.uint32)[:, None]).all()
+    # rows ascending in (d2, position), d2 recomputed with the reference formula, on 1 M sampled rows
+    rows = np.random.default_rng(0).choice(n, 200_000, replace=False)
+    rows.sort()
+    q = pts[rows].astype(np.float32)
+    c = pts[knn[rows]]
+    d = c - q[:, None, :]
+    dx, dy, dz = d[..., 0].astype(np.float64), d[..., 1].astype(np.float64), d[..., 2].astype(np.float64)
+    f32 = np.float32
+    t = (dx * dx + (dy * dy).astype(f32).astype(np.float64)).astype(f32)   # fma(dx,dx,rn(dy*dy))
+    d2 = (dz * dz + t.astype(np.float64)).astype(f32)                       # fma(dz,dz,t)
+    assert (np.diff(d2, axis=1) >= 0).all()
+    tie = np.diff(d2, axis=1) == 0
+    assert (np.diff(knn[rows].astype(np.int64), axis=1)[tie] > 0).all()
+    # exact brute force over all 10 M candidates for 96 sampled queries
+    for q0 in (0, 4_999_968, n - 32):
+        want = oracle.brute(pts, K, q0, q0 + 32)
+        assert np.array_equal(knn[q0:q0 + 32], want)

@@ -1,0 +1,46 @@
+"""GPU parity against the reference's OWN knearests.cu, compiled unmodified for sm_100a
+(oracle/_ref/libref_knearests_k{K}.so, built by oracle/Makefile from /root/reference) and run
+side by side on the same B200 with the same inputs.
+
+Comparison is the canonical one of SURVEY 8c: the reference's layout and tie-breaks depend on atomic
+arrival order (F6, F7), so both sides are mapped to original indices and sorted by
+(d2, original index); rows must then be identical, except for ties exactly at the k/k+1 border.
+"""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def canonical_pair(oracle, kn, pts, K):
+    if not oracle.have_ref(f"libref_knearests_k{K}.so"):
+        pytest.skip("oracle/_ref not built")
+    ref = oracle.RefGpu(K).run(pts)
+    with kn.KnProblem(pts, k=K) as p:
+        p.solve()
+        mine = {"knn": p.get_knearests(), "perm": p.get_permutation(), "dim": p.info.dimx}
+    assert ref["dim"] == mine["dim"]  # same grid sizing, knearests.cu:249
+    assert np.array_equal(np.sort(ref["permutation"]), np.arange(len(pts), dtype=np.uint32))
+    ia, da = oracle.canonical_rows(mine["knn"], mine["perm"], pts)
+    ib, db = oracle.canonical_rows(ref["knn"], ref["permutation"], pts)
+    return ia, da, ib, db
+
+
+@pytest.mark.parametrize("K", [8, 20, 32, 50])
+def test_pts20k_against_reference_gpu(kn, oracle, pts20k, K):
+    ia, da, ib, db = canonical_pair(oracle, kn, pts20k, K)
+    same, ties, bad = oracle.compare_canonical(ia, da, ib, db, ulp_slack=0)
+    assert bad == [] and same + ties == len(pts20k)
+    assert np.array_equal(da, db) or ties > 0  # same distances, bit for bit, wherever the sets agree
+    assert ties <= 3
+
+
+@pytest.mark.parametrize("n,K,seed", [(300_000, 50, 20171004), (900_000, 50, 1), (2_000_000, 20, 2)])
+def test_uniform_against_reference_gpu(kn, oracle, n, K, seed):
+    """configs[1] sizes (300 k / 900 k; the named files are missing from the snapshot, SURVEY F5:
+    uniform substitutes) and a 2 M cloud."""
+    pts = oracle.generate_uniform(n, seed=seed)
+    ia, da, ib, db = canonical_pair(oracle, kn, pts, K)
+    same, ties, bad = oracle.compare_canonical(ia, da, ib, db, ulp_slack=0)
+    assert bad == [] and same + ties == n
+    assert ties < n // 1000
