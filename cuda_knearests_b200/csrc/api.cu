@@ -89,6 +89,15 @@ void free_device_state(knc_problem *p) {
 
 }  // namespace
 
+// Lets the other translation units of the library report through knc_last_error().
+int kn_set_error(int code, const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+    return code;
+}
+
 extern "C" {
 
 const char *knc_last_error(void) { return g_err; }

@@ -58,4 +58,7 @@ cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const Gr
                             int query_begin, int query_count, float radius0_sq, unsigned int *d_knn,
                             unsigned int *d_diag, cudaStream_t st);
 
+// ---- api.cu ------------------------------------------------------------------------------------
+int kn_set_error(int code, const char *fmt, ...);  // records the message knc_last_error() returns
+
 #define KN_BIG_CELL 32  // cells with more points than this are ordered by a whole block, not a thread

@@ -143,6 +143,23 @@ const char *knc_version(void);
  * (the reference has no generator); bit-identical to oracle/knn_oracle.c:kno_generate_uniform. */
 int knc_generate_uniform_device(float *d_xyz, long long first, long long count, uint64_t seed);
 
+/* ---- for callers that must not allocate --------------------------------------------------------
+ * No counterpart in the reference (its every entry point cudaMallocs, knearests.cu:205-231).
+ * The grid build's exclusive scan on its own: d_ptrs[c] = sum of d_counters[0..c), d_ptrs[cells] =
+ * total; both arrays are DEVICE memory the caller owns (cells and cells + 1 ints), `stream` is a
+ * cudaStream_t or NULL.  Meant for programs that have handed the whole GPU to their own memory pool
+ * (frameworks, servers with a fixed arena) or sit in a latency-critical loop, where a cudaMalloc made
+ * by a library is unwelcome: this call allocates nothing, on host or device.  Its scratch (one status
+ * word per 4096 cells) is a static device array inside the library, ~33 KB held on every GPU that
+ * loads the library until exit, which is why at most KNC_NOALLOC_MAX_CELLS cells are accepted (a
+ * 256^3 grid, ~52 M points at the default density); larger sizes return KNC_ERR_INVALID.
+ * The first call on a device resolves the scratch address: make it at start-up, before any stream
+ * capture.  All calls on a device share the scratch; each clears what it uses first, so calls whose GPU
+ * work could overlap (other streams, other threads) race and must be serialised by the caller.
+ * Blocking: returns when `stream` has drained. */
+#define KNC_NOALLOC_MAX_CELLS 16777216LL
+int knc_scan_cells_noalloc(const int *d_counters, long long cells, int *d_ptrs, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
