@@ -47,7 +47,7 @@ class Options(C.Structure):  # knc_options
     _fields_ = [("struct_size", C.c_size_t), ("k", C.c_int), ("density", C.c_float),
                 ("points_on_device", C.c_int), ("grid_dim", C.c_int), ("z_begin", C.c_int),
                 ("z_end", C.c_int), ("own_z_begin", C.c_int), ("own_z_end", C.c_int),
-                ("search_scale", C.c_float)]
+                ("search_scale", C.c_float), ("algorithm", C.c_int)]
 
 
 class Info(C.Structure):  # knc_info
@@ -126,7 +126,7 @@ class KnProblem:
     """
 
     def __init__(self, points, k: int = 0, density: float = 0.0, grid_dim: int = 0, slab=None,
-                 search_scale: float = 0.0):
+                 search_scale: float = 0.0, algorithm: int = 0):
         self._h = C.c_void_p()
         opt = Options()
         opt.struct_size = C.sizeof(Options)
@@ -134,6 +134,7 @@ class KnProblem:
         opt.density = float(density)
         opt.grid_dim = int(grid_dim)
         opt.search_scale = float(search_scale)
+        opt.algorithm = int(algorithm)
         if slab is not None:
             opt.z_begin, opt.z_end, opt.own_z_begin, opt.own_z_end = (int(v) for v in slab)
         if hasattr(points, "is_cuda"):

@@ -152,6 +152,7 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     st = p->stream;
     for (cudaEvent_t &e : p->ev) CU(cudaEventCreate(&e));
     p->k = k; p->density = density; p->search_scale = o.search_scale > 0.f ? o.search_scale : 1.f;
+    p->algorithm = o.algorithm;
     p->z_begin = zb; p->z_end = ze; p->own_z_begin = ozb; p->own_z_end = oze;
     p->dim_global = D; p->cells = cells;
     p->pub.allocated_points = n;
@@ -243,16 +244,19 @@ int knc_solve(knc_problem *p) {
     const double lambda = p->k + 2.5 * sqrt((double)p->k) + 2.0;
     const double r0 = cbrt(3.0 * lambda / (4.0 * M_PI * rho)) * p->search_scale;
     unsigned diag[4] = {0, 0, 0, 0};
+    int *d_retry = NULL;  // scratch of the solve: queries the fast kernel hands to the general kernel
+    const int force_general = p->algorithm == 1;
+    CU(dev_alloc((void **)&d_retry, sizeof(int) * (size_t)(p->query_count > 0 ? p->query_count : 1), st));
     CU(cudaMemsetAsync(p->d_diag, 0, sizeof(unsigned) * 4, st));
     CU(cudaEventRecord(p->ev[2], st));
     CU(kn_launch_query(p->d_points4, p->pub.d_ptrs, g, p->pub.allocated_points, p->k, p->query_begin,
-                       p->query_count, (float)(r0 * r0), p->pub.d_knearests, p->d_diag, st));
+                       p->query_count, (float)(r0 * r0), p->pub.d_knearests, p->d_diag, d_retry, force_general, st));
     CU(cudaEventRecord(p->ev[3], st));
     CU(cudaMemcpyAsync(diag, p->d_diag, sizeof(diag), cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(p->pub.d_cell_max, p->d_diag + 1, sizeof(float), cudaMemcpyDeviceToDevice, st));
     CU(cudaStreamSynchronize(st));  // blocking, like knearests.cu:373
     CU(cudaEventElapsedTime(&p->t.solve_ms, p->ev[2], p->ev[3]));
-    p->t.restarts = diag[0];
+    p->t.restarts = diag[0] + diag[3];  // restarts inside the general kernel + queries retried after the fast one
     memcpy(&p->t.max_radius2, &diag[1], sizeof(float));
     p->solved = 1;
     if (verbose()) {
@@ -261,9 +265,10 @@ int knc_solve(knc_problem *p) {
                 sqrt((double)p->t.max_radius2) / g.w, r0 / g.w, diag[0], p->query_count);
     }
     if (diag[2])
-        return fail(KNC_ERR_HALO, "knc_solve: %u queries reach beyond the halo planes [%d,%d) of this slab", diag[2],
-                    p->z_begin, p->z_end);
+        rc = fail(KNC_ERR_HALO, "knc_solve: %u queries reach beyond the halo planes [%d,%d) of this slab", diag[2],
+                  p->z_begin, p->z_end);
 out:
+    if (d_retry) cudaFreeAsync(d_retry, st);
     return rc;
 }
 

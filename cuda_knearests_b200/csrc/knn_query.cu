@@ -26,8 +26,14 @@
 //    shared memory, slot-major so that a warp's accesses are conflict free.  One unsigned compare
 //    orders by (d2, position): the result is independent of visiting order, i.e. deterministic, and
 //    the row comes out already sorted (the reference needs a heapsort pass, knearests.cu:141).
-//  * The inner loop runs "to the next candidate that passes" before any lane inserts, so the
-//    (expensive, divergent) insertion runs with as many lanes as possible.
+//  * Two kernels.  kn_query_fast_kernel does the common case with warp-uniform control flow: every
+//    lane first turns its rows into a list of point spans (uniform loop over the row table), then all
+//    lanes stream their own spans in one flat loop, one candidate per lane per iteration; candidates
+//    that pass the current bound go to a small per-lane queue and are inserted in bursts, when the
+//    whole warp inserts together.  (v1 walked rows and candidates in per-lane nested loops: 9 of 32
+//    lanes active on average, profiles/r1_query_v1_*.)  A query whose first-guess sphere held fewer
+//    than k points is appended to a retry list, and kn_query_general_kernel -- per-lane nested loops,
+//    restarts, rings beyond the table: exact for anything -- finishes those, densely packed.
 //  * Rows are written through shared memory as one contiguous, coalesced run per block
 //    (the reference writes stride-k, knearests.cu:144-147).
 //
@@ -65,6 +71,8 @@ struct QueryParams {
     GridGeom g;
     int n, k, query_begin, query_count;
     float radius0_sq;
+    int *retry_list;       // sorted positions of the queries the fast kernel could not finish
+    unsigned int *retry_count;
     RowTable tab;
 };
 
@@ -74,156 +82,392 @@ __device__ __forceinline__ float sqrt_approx(float x) {
     return r;
 }
 
+// Per-query geometry shared by both kernels.
+struct QueryGeom {
+    float px, py, pz;   // the query point
+    float tx, fy, fz;   // x in cell units; position inside the own cell in y and z (cell units)
+    float tz;
+    int cj, ck;         // own cell row (global plane index for ck)
+};
+
+__device__ __forceinline__ QueryGeom query_geom(const float4 me, const GridGeom &g) {
+    QueryGeom s;
+    s.px = me.x; s.py = me.y; s.pz = me.z;
+    // same rounding as the build (knearests.cu:23-28): mul.f32, div.rn.f32, floor
+    s.tx = __fdiv_rn(__fmul_rn(me.x, g.Df), 1000.f);
+    const float ty = __fdiv_rn(__fmul_rn(me.y, g.Df), 1000.f);
+    s.tz = __fdiv_rn(__fmul_rn(me.z, g.Df), 1000.f);
+    s.cj = max(0, min((int)floorf(ty), g.D - 1));
+    s.ck = max(g.zb, min((int)floorf(s.tz), g.ze - 1));
+    s.fy = ty - (float)s.cj;
+    s.fz = s.tz - (float)s.ck;
+    return s;
+}
+
+// Conservative squared distance from the query to the x-row (cj+dj, ck+dk) of cells.
+__device__ __forceinline__ float row_lower_bound2(const QueryGeom &s, int dj, int dk, float w) {
+    const float gy = fmaxf(0.f, fmaxf((float)dj - s.fy, s.fy - (float)dj - 1.f));
+    const float gz = fmaxf(0.f, fmaxf((float)dk - s.fz, s.fz - (float)dk - 1.f));
+    const float ly = fmaxf(0.f, fmaf(gy, w, -kMargin)), lz = fmaxf(0.f, fmaf(gz, w, -kMargin));
+    return (ly * ly + lz * lz) * kShrink;
+}
+
+// Cells [ilo, ihi] of a row that can hold a point within sqrt(bound2 - lbyz2) of the query in x.
+__device__ __forceinline__ void row_x_range(const QueryGeom &s, float bound2, float lbyz2, float invw, int D,
+                                            int &ilo, int &ihi) {
+    const float rxc = fmaf(sqrt_approx(bound2 - lbyz2) * kGrow, invw, kMargin * invw + 1e-3f);
+    ilo = max(0, (int)floorf(s.tx - rxc));
+    ihi = min(D - 1, (int)floorf(s.tx + rxc));
+}
+
+__device__ __forceinline__ unsigned long long make_key(const float4 c, const QueryGeom &s, int p) {
+    const float dx = c.x - s.px, dy = c.y - s.py, dz = c.z - s.pz;
+    const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));  // knearests.cu:125 as compiled
+    return ((unsigned long long)__float_as_uint(d2) << 32) | (unsigned)p;
+}
+
+// Sorted insertion into the slot-major list L (stride QB); the worst entry drops off the end.
+template <int QB>
+__device__ __forceinline__ void list_insert(unsigned long long *L, int K, int &cnt, unsigned long long key) {
+    int s;
+    if (cnt < K) s = cnt++; else s = K - 1;
+    while (s > 0) {
+        const unsigned long long e = L[(s - 1) * QB];
+        if (e < key) break;
+        L[s * QB] = e;
+        --s;
+    }
+    L[s * QB] = key;
+}
+
+// Restart counter, largest final radius, slab halo misses (planes that exist globally but are not held).
+__device__ __forceinline__ void report_diag(const QueryParams &P, const QueryGeom &s, bool finished, float kd2,
+                                            unsigned restarts, int tid) {
+    unsigned rad_bits = 0, halo_miss = 0;
+    if (finished) {
+        rad_bits = __float_as_uint(kd2);
+        if (P.g.zb > 0) {
+            const float gap = fmaxf(0.f, (s.tz - (float)P.g.zb) * P.g.w - kMargin);
+            if (gap * gap * kShrink <= kd2) halo_miss = 1;
+        }
+        if (P.g.ze < P.g.D) {
+            const float gap = fmaxf(0.f, ((float)P.g.ze - s.tz) * P.g.w - kMargin);
+            if (gap * gap * kShrink <= kd2) halo_miss = 1;
+        }
+    }
+    const unsigned wr = __reduce_add_sync(0xffffffffu, restarts);
+    const unsigned wm = __reduce_max_sync(0xffffffffu, rad_bits);
+    const unsigned wh = __reduce_add_sync(0xffffffffu, halo_miss);
+    if ((tid & 31) == 0) {
+        if (wr) atomicAdd(P.diag + 0, wr);
+        atomicMax(P.diag + 1, wm);
+        if (wh) atomicAdd(P.diag + 2, wh);
+    }
+}
+
+// ======================================================================================== fast path
+constexpr int kFirstBatch = 9;   // the own row and its 8 neighbours (lower bound 0)
+constexpr int kNextBatch = 8;    // rows per later batch
+constexpr int kSpanSlots = 9;    // spans a lane can hold per batch
+constexpr int kQueueSlots = 8;   // pending candidates per lane between insertion bursts
+constexpr int kChunk = 4;        // candidates a lane takes per lock-step iteration
+
+__device__ __forceinline__ void cswap(unsigned long long &a, unsigned long long &b) {
+    const unsigned long long lo = a < b ? a : b, hi = a < b ? b : a;
+    a = lo; b = hi;
+}
+
 template <int K_T, int QB>
-__global__ void __launch_bounds__(QB) kn_query_kernel(const __grid_constant__ QueryParams P) {
-    extern __shared__ unsigned long long klist[];  // [K][QB]: slot-major, thread-minor
+__global__ void __launch_bounds__(QB) kn_query_fast_kernel(const __grid_constant__ QueryParams P) {
+    extern __shared__ unsigned long long smem[];
     const int K = K_T ? K_T : P.k;
     const int tid = threadIdx.x;
+    unsigned long long *L = smem + tid;                                        // [K][QB] sorted k best
+    int2 *SP = reinterpret_cast<int2 *>(smem + (size_t)K * QB) + tid;          // [kSpanSlots][QB] spans
+    unsigned long long *QU = smem + (size_t)(K + kSpanSlots) * QB + tid;       // [kQueueSlots][QB] pending
     const int D = P.g.D, zb = P.g.zb, ze = P.g.ze;
     const float w = P.g.w, invw = P.g.invw;
     const long long row0 = (long long)blockIdx.x * QB;
     const bool valid = row0 + tid < P.query_count;
     const int q = P.query_begin + (int)min(row0 + tid, (long long)P.query_count - 1);
-    unsigned long long *L = klist + tid;
+    const QueryGeom s = query_geom(__ldg(P.pts + q), P.g);
 
-    const float4 me = __ldg(P.pts + q);
-    const float px = me.x, py = me.y, pz = me.z;
-    // own cell and position inside it, in cell units (same rounding as the build, knearests.cu:23-28)
-    const float tx = __fdiv_rn(__fmul_rn(px, P.g.Df), 1000.f);
-    const float ty = __fdiv_rn(__fmul_rn(py, P.g.Df), 1000.f);
-    const float tz = __fdiv_rn(__fmul_rn(pz, P.g.Df), 1000.f);
-    const int cj = max(0, min((int)floorf(ty), D - 1));
-    const int ck = max(zb, min((int)floorf(tz), ze - 1));
-    const float fy = ty - (float)cj, fz = tz - (float)ck;
-
-    int cnt = 0;
-    unsigned long long kth = ~0ull;
-    float r2 = P.radius0_sq;
+    const float r2 = P.radius0_sq;
+    // Only candidates inside the first-guess sphere are ever held: a full list is then final.
+    unsigned long long kth = ((unsigned long long)__float_as_uint(r2) << 32) | 0xFFFFFFFFu;
     float bound2 = r2;
-    bool pruned = false;
-    unsigned restarts = 0;
+    int cnt = 0, qlen = 0;
 
-    // ---- one x-row of cells -----------------------------------------------------------------------
-    auto scan_row = [&](int dj, int dk) {
-        const int j = cj + dj, k = ck + dk;
-        if (j < 0 || j >= D || k < zb || k >= ze) return;
-        const float gy = fmaxf(0.f, fmaxf((float)dj - fy, fy - (float)dj - 1.f));
-        const float gz = fmaxf(0.f, fmaxf((float)dk - fz, fz - (float)dk - 1.f));
-        const float ly = fmaxf(0.f, fmaf(gy, w, -kMargin)), lz = fmaxf(0.f, fmaf(gz, w, -kMargin));
-        const float lbyz2 = (ly * ly + lz * lz) * kShrink;
-        if (lbyz2 > bound2) { pruned = true; return; }
-        const float rxc = fmaf(sqrt_approx(bound2 - lbyz2) * kGrow, invw, kMargin * invw + 1e-3f);
-        const int ilo = max(0, (int)floorf(tx - rxc)), ihi = min(D - 1, (int)floorf(tx + rxc));
-        if (ilo > 0 || ihi < D - 1) pruned = true;
-        if (ilo > ihi) return;
-        const int row = ((k - zb) * D + j) * D;
-        int p = __ldg(P.ptrs + row + ilo);
-        const int end = __ldg(P.ptrs + row + ihi + 1);
-        if (p >= end) return;
-        float4 c = __ldg(P.pts + p);
-        while (true) {
-            unsigned long long key;
-            bool found;
-            while (true) {  // run to the next candidate that beats the current k-th
-                const float4 nx = __ldg(P.pts + min(p + 1, end - 1));
-                const float dx = c.x - px, dy = c.y - py, dz = c.z - pz;
-                const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
-                key = ((unsigned long long)__float_as_uint(d2) << 32) | (unsigned)p;
-                found = key < kth && p != q;  // self excluded by position, knearests.cu:123
-                c = nx;
-                ++p;
-                if (found || p >= end) break;
-            }
-            if (found) {  // sorted insertion, worst entry drops off the end
-                int s;
-                if (cnt < K) s = cnt++; else s = K - 1;
-                while (s > 0) {
-                    const unsigned long long e = L[(s - 1) * QB];
-                    if (e < key) break;
-                    L[s * QB] = e;
-                    --s;
-                }
-                L[s * QB] = key;
-                if (cnt == K) {
-                    kth = L[(K - 1) * QB];
-                    bound2 = fminf(r2, __uint_as_float((unsigned)(kth >> 32)));
+    // Insertion burst for the whole warp.  Small bursts insert one by one; larger ones sort the
+    // pending keys (19-comparator network in registers) and merge them into the list in ONE backward
+    // pass, whose length is about the same in every lane.
+    auto drain = [&]() {
+        const int m = __reduce_max_sync(0xffffffffu, qlen);
+        if (m == 0) return;
+        if (m <= 2) {
+            for (int i = 0; i < m; ++i) {
+                if (i < qlen) {
+                    const unsigned long long key = QU[i * QB];
+                    if (key < kth) {  // the bound may have tightened since the candidate was queued
+                        list_insert<QB>(L, K, cnt, key);
+                        if (cnt == K) kth = L[(K - 1) * QB];
+                    }
                 }
             }
-            if (p >= end) break;
+        } else {
+            unsigned long long b[kQueueSlots];
+            int nb = 0;
+#pragma unroll
+            for (int u = 0; u < kQueueSlots; ++u) {
+                b[u] = ~0ull;
+                if (u < qlen) {
+                    const unsigned long long key = QU[u * QB];
+                    if (key < kth) { b[u] = key; ++nb; }
+                }
+            }
+            cswap(b[0], b[1]); cswap(b[2], b[3]); cswap(b[4], b[5]); cswap(b[6], b[7]);
+            cswap(b[0], b[2]); cswap(b[1], b[3]); cswap(b[4], b[6]); cswap(b[5], b[7]);
+            cswap(b[1], b[2]); cswap(b[5], b[6]); cswap(b[0], b[4]); cswap(b[3], b[7]);
+            cswap(b[1], b[5]); cswap(b[2], b[6]);
+            cswap(b[1], b[4]); cswap(b[3], b[6]);
+            cswap(b[2], b[4]); cswap(b[3], b[5]);
+            cswap(b[3], b[4]);
+#pragma unroll
+            for (int u = 0; u < kQueueSlots; ++u) QU[u * QB] = b[u];
+            int i = cnt - 1, j = nb - 1, o = cnt + nb - 1;
+            unsigned long long e = i >= 0 ? L[i * QB] : 0ull;
+            unsigned long long bj = j >= 0 ? QU[j * QB] : 0ull;
+            while (j >= 0) {  // merge from the back; entries that fall beyond slot K-1 are dropped
+                const bool from_list = i >= 0 && e > bj;
+                if (o < K) L[o * QB] = from_list ? e : bj;
+                if (from_list) { --i; e = i >= 0 ? L[i * QB] : 0ull; }
+                else { --j; bj = j >= 0 ? QU[j * QB] : 0ull; }
+                --o;
+            }
+            cnt = min(K, cnt + nb);
+            if (cnt == K) kth = L[(K - 1) * QB];
         }
+        if (cnt == K) bound2 = __uint_as_float((unsigned)(kth >> 32));
+        qlen = 0;
     };
 
-    bool done = !valid;
-    while (!done) {
-        cnt = 0; kth = ~0ull; bound2 = r2; pruned = false;
-        bool table_exhausted = true;
-        for (int e = 0; e < P.tab.n; ++e) {  // rows nearest-first
-            if (P.tab.lb2[e] > bound2) { pruned = true; table_exhausted = false; break; }
-            scan_row(P.tab.dj[e], P.tab.dk[e]);
-        }
-        if (table_exhausted) {  // rare: beyond the table, plain square rings of rows
-            const int rmax = max(max(cj, D - 1 - cj), max(ck - zb, ze - 1 - ck));
-            for (int r = kTableRing + 1; r <= rmax; ++r) {
-                const float lb = fmaxf(0.f, (float)(r - 1) * w - kMargin);
-                if (lb * lb * kShrink > bound2) { pruned = true; break; }
-                for (int dk = -r; dk <= r; ++dk)
-                    for (int dj = -r; dj <= r; dj += (abs(dk) == r ? 1 : 2 * r)) scan_row(dj, dk);
+    int e0 = 0, e1 = min(kFirstBatch, P.tab.n);
+    while (true) {
+        const bool want = valid && P.tab.lb2[e0] <= bound2;  // table is sorted by lower bound
+        if (!__any_sync(0xffffffffu, want)) break;
+
+        // ---- 1. rows e0..e1 -> spans of candidate positions (uniform loop, 4 rows' pointers in flight)
+        int nsp = 0;
+        for (int e = e0; e < e1; e += 4) {
+            int alo[4], ahi[4];
+            bool ok[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                ok[u] = false;
+                const int ee = e + u;
+                if (ee < e1 && want && P.tab.lb2[ee] <= bound2) {
+                    const int dj = P.tab.dj[ee], dk = P.tab.dk[ee];
+                    const int j = s.cj + dj, k = s.ck + dk;
+                    if (j >= 0 && j < D && k >= zb && k < ze) {
+                        const float lbyz2 = row_lower_bound2(s, dj, dk, w);
+                        if (lbyz2 <= bound2) {
+                            int ilo, ihi;
+                            row_x_range(s, bound2, lbyz2, invw, D, ilo, ihi);
+                            const int row = ((k - zb) * D + j) * D;
+                            alo[u] = row + ilo;
+                            ahi[u] = row + ihi + 1;
+                            ok[u] = ilo <= ihi;
+                        }
+                    }
+                }
             }
+            int b4[4], e4[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) { b4[u] = __ldg(P.ptrs + alo[u]); e4[u] = __ldg(P.ptrs + ahi[u]); }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u] && b4[u] < e4[u]) { SP[nsp * QB] = make_int2(b4[u], e4[u]); ++nsp; }
         }
-        const float kd2 = __uint_as_float((unsigned)(kth >> 32));
-        if ((cnt == K && kd2 <= r2) || !pruned) {
-            done = true;  // everything within the k-th distance was searched, or the whole grid was
-        } else {
-            r2 = (cnt == K) ? kd2 : r2 * 2.25f;  // the k-th found is a proven sufficient radius
-            ++restarts;
+
+        // ---- 2. every lane streams its own spans, kChunk candidates per iteration, in lock step
+        int sp = 0, p = 0, end = 0;
+        if (nsp > 0) { const int2 t = SP[0]; p = t.x; end = t.y; sp = 1; }
+        while (__any_sync(0xffffffffu, p < end)) {
+            float4 c[kChunk];
+#pragma unroll
+            for (int u = 0; u < kChunk; ++u) {
+                c[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (p + u < end) c[u] = __ldg(P.pts + p + u);
+            }
+#pragma unroll
+            for (int u = 0; u < kChunk; ++u) {
+                if (p + u < end) {
+                    const unsigned long long key = make_key(c[u], s, p + u);
+                    if (key < kth && p + u != q) { QU[qlen * QB] = key; ++qlen; }  // self excluded, knearests.cu:123
+                }
+            }
+            // the unused .w lanes stay allocated until here: otherwise they are recycled at once and the
+            // next instruction that writes them waits for the loads (seen in profiles/r1_query_v2*)
+            asm volatile("" ::"f"(c[0].w), "f"(c[1].w), "f"(c[2].w), "f"(c[3].w));
+            p += kChunk;
+            if (p >= end && sp < nsp) { const int2 t = SP[sp * QB]; p = t.x; end = t.y; ++sp; }
+            if (__any_sync(0xffffffffu, qlen > kQueueSlots - kChunk)) drain();
         }
+        drain();
+
+        e0 = e1;
+        if (e0 >= P.tab.n) break;  // the launcher only takes this path when the table covers the sphere
+        e1 = min(e0 + kNextBatch, P.tab.n);
     }
 
-    // ---- diagnostics: restarts, largest final radius, slab halo misses ------------------------------
-    {
-        unsigned rad_bits = 0, halo_miss = 0;
-        if (valid) {
-            const float kd2 = (cnt == K) ? __uint_as_float((unsigned)(kth >> 32)) : FLT_MAX;
-            rad_bits = __float_as_uint(kd2);
-            // slab mode: planes below zb / above ze exist globally but are not held here
-            if (zb > 0) {
-                const float gap = fmaxf(0.f, (tz - (float)zb) * w - kMargin);
-                if (gap * gap * kShrink <= kd2) halo_miss = 1;
-            }
-            if (ze < D) {
-                const float gap = fmaxf(0.f, ((float)ze - tz) * w - kMargin);
-                if (gap * gap * kShrink <= kd2) halo_miss = 1;
-            }
-        }
-        const unsigned wr = __reduce_add_sync(0xffffffffu, restarts);
-        const unsigned wm = __reduce_max_sync(0xffffffffu, rad_bits);
-        const unsigned wh = __reduce_add_sync(0xffffffffu, halo_miss);
-        if ((tid & 31) == 0) {
-            if (wr) atomicAdd(P.diag + 0, wr);
-            atomicMax(P.diag + 1, wm);
-            if (wh) atomicAdd(P.diag + 2, wh);
-        }
-    }
+    // fewer than k points inside the first-guess sphere: hand the query to the general kernel
+    const bool finished = valid && cnt == K;
+    if (valid && !finished) P.retry_list[atomicAdd(P.retry_count, 1u)] = q;
+    report_diag(P, s, finished, finished ? __uint_as_float((unsigned)(kth >> 32)) : 0.f, 0u, tid);
 
-    // ---- coalesced row output ------------------------------------------------------------------------
-    for (int s = cnt; s < K; ++s) L[s * QB] = ~0ull;  // low word = UINT_MAX = "no such neighbour"
+    // ---- coalesced row output --------------------------------------------------------------------
+    for (int t = cnt; t < K; ++t) L[t * QB] = ~0ull;  // low word = UINT_MAX = "no such neighbour"
     __syncthreads();
     const int rows = (int)min((long long)QB, (long long)P.query_count - row0);
     unsigned int *out = P.knn + row0 * K;
     for (int idx = tid; idx < rows * K; idx += QB) {
-        const int t = idx / K, s = idx - t * K;
-        out[idx] = (unsigned)klist[s * QB + t];
+        const int t = idx / K, sl = idx - t * K;
+        out[idx] = (unsigned)smem[sl * QB + t];
+    }
+}
+
+// ===================================================================================== general path
+// Per-lane nested loops over rows and candidates, restarts with a growing radius, plain square rings
+// of rows beyond the table: exact for any input.  RETRY = false: one thread per query of the range
+// (used when the fast path does not apply); RETRY = true: the queries listed by the fast kernel.
+template <int K_T, int QB, bool RETRY>
+__global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_constant__ QueryParams P) {
+    extern __shared__ unsigned long long smem[];  // [K][QB]: slot-major, thread-minor
+    const int K = K_T ? K_T : P.k;
+    const int tid = threadIdx.x;
+    const int D = P.g.D, zb = P.g.zb, ze = P.g.ze;
+    const float w = P.g.w, invw = P.g.invw;
+    unsigned long long *L = smem + tid;
+    const long long total = RETRY ? (long long)*P.retry_count : (long long)P.query_count;
+    const long long stride = (long long)gridDim.x * QB;
+
+    for (long long row0 = (long long)blockIdx.x * QB; row0 < total; row0 += stride) {
+        const bool valid = row0 + tid < total;
+        const long long slot = min(row0 + tid, total - 1);
+        const int q = RETRY ? P.retry_list[slot] : P.query_begin + (int)slot;
+        const QueryGeom s = query_geom(__ldg(P.pts + q), P.g);
+
+        int cnt = 0;
+        unsigned long long kth = ~0ull;
+        float r2 = RETRY ? P.radius0_sq * 2.25f : P.radius0_sq;
+        float bound2 = r2;
+        bool pruned = false;
+        unsigned restarts = 0;
+
+        auto scan_row = [&](int dj, int dk) {
+            const int j = s.cj + dj, k = s.ck + dk;
+            if (j < 0 || j >= D || k < zb || k >= ze) return;
+            const float lbyz2 = row_lower_bound2(s, dj, dk, w);
+            if (lbyz2 > bound2) { pruned = true; return; }
+            int ilo, ihi;
+            row_x_range(s, bound2, lbyz2, invw, D, ilo, ihi);
+            if (ilo > 0 || ihi < D - 1) pruned = true;
+            if (ilo > ihi) return;
+            const int row = ((k - zb) * D + j) * D;
+            int p = __ldg(P.ptrs + row + ilo);
+            const int end = __ldg(P.ptrs + row + ihi + 1);
+            if (p >= end) return;
+            float4 c = __ldg(P.pts + p);
+            while (true) {
+                unsigned long long key;
+                bool found;
+                while (true) {  // run to the next candidate that beats the current k-th
+                    const float4 nx = __ldg(P.pts + min(p + 1, end - 1));
+                    key = make_key(c, s, p);
+                    found = key < kth && p != q;  // self excluded by position, knearests.cu:123
+                    c = nx;
+                    ++p;
+                    if (found || p >= end) break;
+                }
+                if (found) {
+                    list_insert<QB>(L, K, cnt, key);
+                    if (cnt == K) {
+                        kth = L[(K - 1) * QB];
+                        bound2 = fminf(r2, __uint_as_float((unsigned)(kth >> 32)));
+                    }
+                }
+                if (p >= end) break;
+            }
+        };
+
+        bool done = !valid;
+        while (!done) {
+            cnt = 0; kth = ~0ull; bound2 = r2; pruned = false;
+            bool table_exhausted = true;
+            for (int e = 0; e < P.tab.n; ++e) {  // rows nearest-first
+                if (P.tab.lb2[e] > bound2) { pruned = true; table_exhausted = false; break; }
+                scan_row(P.tab.dj[e], P.tab.dk[e]);
+            }
+            if (table_exhausted) {  // beyond the table: plain square rings of rows
+                const int rmax = max(max(s.cj, D - 1 - s.cj), max(s.ck - zb, ze - 1 - s.ck));
+                for (int r = kTableRing + 1; r <= rmax; ++r) {
+                    const float lb = fmaxf(0.f, (float)(r - 1) * w - kMargin);
+                    if (lb * lb * kShrink > bound2) { pruned = true; break; }
+                    for (int dk = -r; dk <= r; ++dk)
+                        for (int dj = -r; dj <= r; dj += (abs(dk) == r ? 1 : 2 * r)) scan_row(dj, dk);
+                }
+            }
+            const float kd2 = __uint_as_float((unsigned)(kth >> 32));
+            if ((cnt == K && kd2 <= r2) || !pruned) {
+                done = true;  // everything within the k-th distance was searched, or the whole grid was
+            } else {
+                r2 = (cnt == K) ? kd2 : r2 * 2.25f;  // the k-th found is a proven sufficient radius
+                ++restarts;
+            }
+        }
+        report_diag(P, s, valid, (cnt == K) ? __uint_as_float((unsigned)(kth >> 32)) : FLT_MAX, restarts, tid);
+
+        for (int t = cnt; t < K; ++t) L[t * QB] = ~0ull;  // low word = UINT_MAX = "no such neighbour"
+        if (RETRY) {  // scattered rows: each thread writes its own
+            if (valid) {
+                unsigned int *out = P.knn + (long long)(q - P.query_begin) * K;
+                for (int t = 0; t < K; ++t) out[t] = (unsigned)L[t * QB];
+            }
+        } else {      // contiguous rows: one coalesced run per block
+            __syncthreads();
+            const int rows = (int)min((long long)QB, total - row0);
+            unsigned int *out = P.knn + row0 * K;
+            for (int idx = tid; idx < rows * K; idx += QB) {
+                const int t = idx / K, sl = idx - t * K;
+                out[idx] = (unsigned)smem[sl * QB + t];
+            }
+            __syncthreads();
+        }
     }
 }
 
 template <int K_T, int QB>
-cudaError_t launch(const QueryParams &P, cudaStream_t st) {
-    const size_t smem = sizeof(unsigned long long) * (size_t)P.k * QB;
-    cudaError_t e = cudaFuncSetAttribute(kn_query_kernel<K_T, QB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)smem);
-    if (e != cudaSuccess) return e;
+cudaError_t launch(const QueryParams &P, bool fast, cudaStream_t st) {
+    const size_t list_bytes = sizeof(unsigned long long) * (size_t)P.k * QB;
     const unsigned blocks = (unsigned)(((long long)P.query_count + QB - 1) / QB);
-    kn_query_kernel<K_T, QB><<<blocks, QB, smem, st>>>(P);
+    cudaError_t e;
+    if (fast) {
+        const size_t smem = list_bytes + sizeof(unsigned long long) * (size_t)(kSpanSlots + kQueueSlots) * QB;
+        e = cudaFuncSetAttribute(kn_query_fast_kernel<K_T, QB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        kn_query_fast_kernel<K_T, QB><<<blocks, QB, smem, st>>>(P);
+        e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)list_bytes);
+        if (e != cudaSuccess) return e;
+        const unsigned retry_blocks = blocks < 148u * 8u ? blocks : 148u * 8u;  // loops over the retry list
+        kn_query_general_kernel<K_T, QB, true><<<retry_blocks, QB, list_bytes, st>>>(P);
+    } else {
+        e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)list_bytes);
+        if (e != cudaSuccess) return e;
+        kn_query_general_kernel<K_T, QB, false><<<blocks, QB, list_bytes, st>>>(P);
+    }
     return cudaGetLastError();
 }
 
@@ -260,21 +504,27 @@ void fill_table(RowTable &t, float w) {
 
 cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const GridGeom &g, int n, int k,
                             int query_begin, int query_count, float radius0_sq, unsigned int *d_knn,
-                            unsigned int *d_diag, cudaStream_t st) {
+                            unsigned int *d_diag, int *d_retry_list, int force_general, cudaStream_t st) {
     if (query_count <= 0) return cudaSuccess;
     QueryParams P;
     P.pts = d_points4; P.ptrs = d_ptrs; P.knn = d_knn; P.diag = d_diag; P.g = g;
     P.n = n; P.k = k; P.query_begin = query_begin; P.query_count = query_count;
     P.radius0_sq = radius0_sq;
+    P.retry_list = d_retry_list;
+    P.retry_count = d_diag + 3;
     fill_table(P.tab, g.w);
+    // The fast kernel searches table rows only: usable when every row outside the table is provably
+    // farther than the first-guess radius.
+    const float beyond = fmaxf(0.f, (float)kTableRing * g.w - kMargin);
+    const bool fast = !force_general && d_retry_list && radius0_sq < beyond * beyond * kShrink;
     switch (k) {
-        case 8: return launch<8, 128>(P, st);
-        case 20: return launch<20, 128>(P, st);
-        case 32: return launch<32, 128>(P, st);
-        case 50: return launch<50, 128>(P, st);
+        case 8: return launch<8, 128>(P, fast, st);
+        case 20: return launch<20, 128>(P, fast, st);
+        case 32: return launch<32, 128>(P, fast, st);
+        case 50: return launch<50, 128>(P, fast, st);
         default: break;
     }
-    if (k <= 96) return launch<0, 128>(P, st);
-    if (k <= 192) return launch<0, 64>(P, st);
-    return launch<0, 32>(P, st);
+    if (k <= 96) return launch<0, 128>(P, fast, st);
+    if (k <= 192) return launch<0, 64>(P, fast, st);
+    return launch<0, 32>(P, fast, st);
 }

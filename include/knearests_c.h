@@ -55,6 +55,7 @@ typedef struct {
     int z_begin, z_end;
     int own_z_begin, own_z_end;
     float search_scale;     /* tuning: multiplies the first-guess search radius; default 1             */
+    int algorithm;          /* 0 = automatic (fast kernel + retry), 1 = general kernel only (testing)  */
 } knc_options;
 
 /* What the handle holds; device pointers are valid until knc_free. */

@@ -70,6 +70,25 @@ def test_other_grid_densities(kn, oracle, density):
     assert np.array_equal(res["knn"], g.knn_exact(20))
 
 
+@pytest.mark.parametrize("K", [8, 20, 50, 77])
+def test_general_kernel_alone_gives_the_same_rows(kn, oracle, K):
+    """algorithm=1 runs every query through the general kernel (the one that also serves the retries
+    of the fast kernel); the total order makes both paths produce identical rows."""
+    pts = oracle.generate_uniform(120_000, seed=13)
+    a = run_engine(kn, pts, K)
+    b = run_engine(kn, pts, K, algorithm=1)
+    assert np.array_equal(a["knn"], b["knn"])
+    assert np.array_equal(a["knn"], oracle.Grid(pts).knn_exact(K))
+
+
+def test_search_radius_guess_does_not_change_rows(kn, oracle):
+    pts = oracle.generate_uniform(150_000, seed=14)
+    want = oracle.Grid(pts).knn_exact(20)
+    for scale in (0.3, 0.7, 1.0, 1.6, 3.0, 6.0):  # tiny guess: everything retried; huge: beyond the row table
+        r = run_engine(kn, pts, 20, search_scale=scale)
+        assert np.array_equal(r["knn"], want), scale
+
+
 def test_device_input_equals_host_input(kn, oracle):
     import torch
     n = 250_000
