@@ -1,0 +1,202 @@
+// slab_route.cu -- multi-GPU plumbing on the device: route points to the z-slab owners that need them
+// (owner + halo), and translate finished neighbour rows to global point ids.
+//
+// No reference counterpart: the reference is single-GPU.  This is the device half of the
+// one exchange step of SURVEY 8e; the collective itself (NCCL all-to-all) is issued by the caller
+// (cuda_knearests_b200/slabs.py) on the buffers written here.
+//
+// kn_route_*: STABLE multi-split.  Rank d must receive every local point whose cell plane lies in
+// [zsplit[d] - halo, zsplit[d+1] + halo); a point near a slab border goes to two (rarely three)
+// ranks.  Records leave grouped by destination and, inside a group, in input order -- so that a
+// receiver that concatenates the groups of ranks 0..W-1 (each holding an index-contiguous chunk of
+// the cloud) sees its slab in global index order, and the engine's stable cell sort then yields
+// exactly the single-GPU order (and therefore bit-identical rows).
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "kn_internal.h"
+
+namespace {
+
+constexpr int kRouteThreads = 256;
+constexpr int kMaxRanks = 32;
+
+struct RoutePlan {
+    int nranks;
+    int lo[kMaxRanks];  // first plane rank d wants
+    int hi[kMaxRanks];  // one past the last plane rank d wants
+};
+
+__device__ __forceinline__ int plane_of(float z, float Df, int D) {
+    // cellFromPoint, z axis (knearests.cu:25,28) -- same rounding as the grid build
+    const int c = (int)floorf(__fdiv_rn(__fmul_rn(z, Df), 1000.f));
+    return max(0, min(c, D - 1));
+}
+
+__device__ __forceinline__ unsigned dest_mask(int plane, const RoutePlan &pl) {
+    unsigned m = 0;
+    for (int d = 0; d < pl.nranks; ++d)
+        if (plane >= pl.lo[d] && plane < pl.hi[d]) m |= 1u << d;
+    return m;
+}
+
+// per block and destination: how many of the block's points go there.  counts[d * nblocks + block]
+__global__ void __launch_bounds__(kRouteThreads)
+kn_route_count_kernel(const float *__restrict__ xyz, int n, float Df, int D, const __grid_constant__ RoutePlan pl,
+                      int nblocks, int *__restrict__ counts) {
+    __shared__ int s_cnt[kMaxRanks];
+    const int tid = threadIdx.x;
+    if (tid < kMaxRanks) s_cnt[tid] = 0;
+    __syncthreads();
+    const long long i = (long long)blockIdx.x * kRouteThreads + tid;
+    const unsigned m = i < n ? dest_mask(plane_of(__ldg(xyz + 3 * i + 2), Df, D), pl) : 0u;
+    for (int d = 0; d < pl.nranks; ++d) {
+        const unsigned b = __ballot_sync(0xffffffffu, (m >> d) & 1u);
+        if ((tid & 31) == 0 && b) atomicAdd(&s_cnt[d], __popc(b));
+    }
+    __syncthreads();
+    if (tid < pl.nranks) counts[(size_t)tid * nblocks + blockIdx.x] = s_cnt[tid];
+}
+
+// one block per destination: exclusive scan of its row of per-block counts, total to totals[d]
+__global__ void __launch_bounds__(1024) kn_route_scan_kernel(int *counts, int nblocks, long long *totals) {
+    __shared__ long long s_warp[32];
+    __shared__ long long s_carry;
+    int *row = counts + (size_t)blockIdx.x * nblocks;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < nblocks; base += 1024) {
+        const int idx = base + tid;
+        const long long v = idx < nblocks ? row[idx] : 0;
+        long long incl = v;
+        for (int d = 1; d < 32; d <<= 1) {
+            const long long t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        long long off = s_carry;
+        for (int wq = 0; wq < warp; ++wq) off += s_warp[wq];
+        if (idx < nblocks) row[idx] = (int)(off + incl - v);  // fits: at most n < 2^31 records per destination
+        __syncthreads();
+        if (tid == 1023) s_carry = off + incl;
+        __syncthreads();
+    }
+    if (tid == 0) totals[blockIdx.x] = s_carry;
+}
+
+// stable scatter: position = base[d] + block offset + rank among the block's earlier points
+__global__ void __launch_bounds__(kRouteThreads)
+kn_route_scatter_kernel(const float *__restrict__ xyz, int n, unsigned first_id, float Df, int D,
+                        const __grid_constant__ RoutePlan pl, int nblocks, const int *__restrict__ offsets,
+                        const long long *__restrict__ base, float *__restrict__ out_xyz,
+                        unsigned *__restrict__ out_id) {
+    __shared__ int s_warp[kMaxRanks][kRouteThreads / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const long long i = (long long)blockIdx.x * kRouteThreads + tid;
+    float x = 0.f, y = 0.f, z = 0.f;
+    unsigned m = 0;
+    if (i < n) {
+        x = __ldg(xyz + 3 * i); y = __ldg(xyz + 3 * i + 1); z = __ldg(xyz + 3 * i + 2);
+        m = dest_mask(plane_of(z, Df, D), pl);
+    }
+    for (int d = 0; d < pl.nranks; ++d) {
+        const unsigned b = __ballot_sync(0xffffffffu, (m >> d) & 1u);
+        if (lane == 0) s_warp[d][warp] = __popc(b);
+    }
+    __syncthreads();
+    for (int d = 0; d < pl.nranks; ++d) {
+        const unsigned b = __ballot_sync(0xffffffffu, (m >> d) & 1u);
+        if ((m >> d) & 1u) {
+            int before = __popc(b & ((1u << lane) - 1u));
+            for (int wq = 0; wq < warp; ++wq) before += s_warp[d][wq];
+            const long long pos = base[d] + offsets[(size_t)d * nblocks + blockIdx.x] + before;
+            out_xyz[3 * pos] = x; out_xyz[3 * pos + 1] = y; out_xyz[3 * pos + 2] = z;
+            out_id[pos] = first_id + (unsigned)i;
+        }
+    }
+}
+
+// rows[r*k + j] = ids[perm[knn[r*k + j]]], query_ids[r] = ids[perm[query_begin + r]]
+__global__ void kn_rows_to_global_kernel(const unsigned *__restrict__ knn, const unsigned *__restrict__ perm,
+                                         const unsigned *__restrict__ ids, int query_begin, long long total, int k,
+                                         unsigned *__restrict__ out_rows, unsigned *__restrict__ out_query_ids) {
+    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= total) return;
+    const unsigned v = __ldg(knn + e);
+    out_rows[e] = v == KNC_EMPTY ? KNC_EMPTY : __ldg(ids + __ldg(perm + v));
+    const long long r = e / k;
+    if (out_query_ids && e - r * k == 0) out_query_ids[r] = __ldg(ids + __ldg(perm + query_begin + r));
+}
+
+}  // namespace
+
+extern "C" int knc_slab_route(const float *d_xyz, int n, unsigned int first_id, int grid_dim, int nranks,
+                              const int *zsplit, int halo, float *d_out_xyz, unsigned int *d_out_id,
+                              long long capacity, long long *out_counts) {
+    if (!d_xyz || !zsplit || !d_out_xyz || !d_out_id || !out_counts || n < 0 || grid_dim < 1 || halo < 0)
+        return kn_set_error(KNC_ERR_INVALID, "knc_slab_route: bad argument");
+    if (nranks < 1 || nranks > kMaxRanks)
+        return kn_set_error(KNC_ERR_INVALID, "knc_slab_route: nranks = %d, supported 1..%d", nranks, kMaxRanks);
+    RoutePlan pl;
+    pl.nranks = nranks;
+    for (int d = 0; d < nranks; ++d) {
+        if (zsplit[d] > zsplit[d + 1] || zsplit[0] != 0 || zsplit[nranks] != grid_dim)
+            return kn_set_error(KNC_ERR_INVALID, "knc_slab_route: zsplit must rise from 0 to grid_dim");
+        pl.lo[d] = zsplit[d] - halo;
+        pl.hi[d] = zsplit[d + 1] + halo;
+        if (zsplit[d] == zsplit[d + 1]) pl.lo[d] = pl.hi[d] = 0;  // an empty slab wants nothing
+    }
+    for (int d = 0; d < nranks; ++d) out_counts[d] = 0;
+    if (n == 0) return KNC_OK;
+    const int nblocks = (n + kRouteThreads - 1) / kRouteThreads;
+    int *d_counts = nullptr;
+    long long *d_tot = nullptr;  // [nranks] totals, then [nranks] bases
+    long long h[2 * kMaxRanks];
+    cudaStream_t st = 0;
+    cudaError_t e = cudaMallocAsync((void **)&d_counts, sizeof(int) * (size_t)nranks * nblocks, st);
+    if (e == cudaSuccess) e = cudaMallocAsync((void **)&d_tot, sizeof(long long) * 2 * kMaxRanks, st);
+    if (e == cudaSuccess) {
+        kn_route_count_kernel<<<nblocks, kRouteThreads, 0, st>>>(d_xyz, n, (float)grid_dim, grid_dim, pl, nblocks, d_counts);
+        kn_route_scan_kernel<<<nranks, 1024, 0, st>>>(d_counts, nblocks, d_tot);
+        e = cudaMemcpyAsync(h, d_tot, sizeof(long long) * nranks, cudaMemcpyDeviceToHost, st);
+    }
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    int rc = KNC_OK;
+    if (e == cudaSuccess) {
+        long long run = 0;
+        for (int d = 0; d < nranks; ++d) { out_counts[d] = h[d]; h[kMaxRanks + d] = run; run += h[d]; }
+        if (run > capacity) {
+            rc = kn_set_error(KNC_ERR_NOMEM, "knc_slab_route: %lld records to send, output capacity %lld", run, capacity);
+        } else {
+            e = cudaMemcpyAsync(d_tot + kMaxRanks, h + kMaxRanks, sizeof(long long) * nranks, cudaMemcpyHostToDevice, st);
+            if (e == cudaSuccess) {
+                kn_route_scatter_kernel<<<nblocks, kRouteThreads, 0, st>>>(d_xyz, n, first_id, (float)grid_dim, grid_dim, pl,
+                                                                          nblocks, d_counts, d_tot + kMaxRanks, d_out_xyz,
+                                                                          d_out_id);
+                e = cudaGetLastError();
+            }
+            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        }
+    }
+    if (d_counts) cudaFreeAsync(d_counts, st);
+    if (d_tot) cudaFreeAsync(d_tot, st);
+    if (e != cudaSuccess) return kn_set_error(KNC_ERR_CUDA, "knc_slab_route: %s", cudaGetErrorString(e));
+    return rc;
+}
+
+extern "C" int knc_get_knearests_global(knc_problem *p, const unsigned int *d_ids, unsigned int *d_out_rows,
+                                        unsigned int *d_out_query_ids) {
+    if (!p || !d_ids || !d_out_rows) return kn_set_error(KNC_ERR_INVALID, "knc_get_knearests_global: NULL argument");
+    if (!p->solved) return kn_set_error(KNC_ERR_STATE, "knc_get_knearests_global: call knc_solve first");
+    const long long total = (long long)p->query_count * p->k;
+    if (total > 0) {
+        kn_rows_to_global_kernel<<<(unsigned)((total + 255) / 256), 256, 0, p->stream>>>(
+            p->pub.d_knearests, p->pub.d_permutation, d_ids, p->query_begin, total, p->k, d_out_rows, d_out_query_ids);
+        cudaError_t e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+        if (e != cudaSuccess) return kn_set_error(KNC_ERR_CUDA, "knc_get_knearests_global: %s", cudaGetErrorString(e));
+    }
+    return KNC_OK;
+}

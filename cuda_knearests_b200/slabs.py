@@ -1,0 +1,240 @@
+"""slabs -- z-slab sharding of one kNN problem over the GPUs of a node, one process per GPU.
+
+No reference counterpart (the reference is single-GPU); this is SURVEY 8e.  Every rank
+holds an index-contiguous chunk of the cloud.  One GLOBAL grid is sized from the total point count
+(knearests.cu:249); rank r owns the cell planes [zsplit[r], zsplit[r+1]) and needs `halo` more planes
+on either side as read-only candidates.  One exchange step moves the points:
+
+  knc_slab_route (CUDA, stable multi-split by destination)  ->  all-to-all (NCCL over NVLink; gloo in
+  the CPU tests)  ->  knc_prepare_ex(slab) + knc_solve per rank  ->  knc_get_knearests_global
+
+Because the route is stable and ranks hold rising index ranges, a rank receives its slab in global index
+order, the engine's stable cell sort reproduces the single-GPU order, and the rows are bit-identical to
+the single-GPU rows (tests/test_multi_gpu.py).  The engine itself checks that the halo was wide
+enough (KNC_ERR_HALO); if any rank reports a miss, all ranks widen the halo and repeat.
+
+PyTorch is used for buffers and torch.distributed only.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import time
+
+import numpy as np
+
+
+def grid_and_split(n_total: int, world: int, density: float = 3.1):
+    """Global grid resolution and plane ownership: zsplit[r] = r * D // world."""
+    import cuda_knearests_b200 as K
+    D = K.grid_dim(n_total, density)
+    return D, [(r * D) // world for r in range(world + 1)]
+
+
+def halo_planes(k: int, density: float = 3.1) -> int:
+    """Planes of halo on each side: 1.75 x the first-guess search radius, in cells (SURVEY 8e table:
+    k = 8 / 20 / 32 / 50 -> 2 / 3 / 3 / 4).  Verified after the solve, widened if it was not enough."""
+    lam = k + 2.5 * math.sqrt(k) + 2.0
+    r0_cells = (3.0 * lam / (4.0 * math.pi * density)) ** (1.0 / 3.0)
+    return max(2, math.ceil(1.75 * r0_cells))
+
+
+def held_planes(zsplit, rank: int, halo: int, D: int):
+    """(z_begin, z_end, own_z_begin, own_z_end) of a rank: what knc_options wants."""
+    lo, hi = zsplit[rank], zsplit[rank + 1]
+    return max(0, lo - halo), min(D, hi + halo), lo, hi
+
+
+def exchange(send_xyz, send_ids, send_counts, group=None):
+    """The collective of the path: variable-size all-to-all of (xyz, id) records grouped by destination.
+    Works on CUDA tensors (NCCL) and CPU tensors (gloo).  Returns (recv_xyz [m,3], recv_ids [m],
+    recv_counts): the groups of ranks 0..W-1 concatenated in rank order."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group)
+    dev = send_xyz.device
+    sc = torch.tensor(list(send_counts), dtype=torch.int64, device=dev)
+    rc = torch.empty(world, dtype=torch.int64, device=dev)
+    dist.all_to_all_single(rc, sc, group=group)
+    recv_counts = [int(v) for v in rc.tolist()]
+    m = sum(recv_counts)
+    recv_xyz = torch.empty((m, 3), dtype=send_xyz.dtype, device=dev)
+    recv_ids = torch.empty((m,), dtype=send_ids.dtype, device=dev)
+    total = sum(send_counts)
+    dist.all_to_all_single(recv_xyz, send_xyz[:total].contiguous(), recv_counts, list(send_counts), group=group)
+    dist.all_to_all_single(recv_ids, send_ids[:total].contiguous(), recv_counts, list(send_counts), group=group)
+    return recv_xyz, recv_ids, recv_counts
+
+
+def route_device(local_xyz, first_id: int, D: int, zsplit, halo: int):
+    """knc_slab_route on the current device.  Returns (send_xyz, send_ids, counts)."""
+    import torch
+    import cuda_knearests_b200 as K
+    L = K.lib()
+    n = local_xyz.shape[0]
+    world = len(zsplit) - 1
+    cap = int(n * 1.5) + 4096
+    zs = (C.c_int * (world + 1))(*zsplit)
+    counts = (C.c_longlong * world)()
+    while True:
+        out_xyz = torch.empty((cap, 3), dtype=torch.float32, device=local_xyz.device)
+        out_ids = torch.empty((cap,), dtype=torch.int32, device=local_xyz.device)
+        torch.cuda.current_stream().synchronize()
+        rc = L.knc_slab_route(C.c_void_p(local_xyz.data_ptr()), n, first_id, D, world, zs, halo,
+                              C.c_void_p(out_xyz.data_ptr()), C.c_void_p(out_ids.data_ptr()), cap, counts)
+        if rc == 3 and sum(counts) > cap:  # KNC_ERR_NOMEM: groups larger than guessed
+            cap = int(sum(counts)) + 4096
+            continue
+        K._check(rc)
+        return out_xyz, out_ids, [int(c) for c in counts]
+
+
+class SlabRows:
+    """Result of one rank: rows of GLOBAL ids for the queries this rank owns."""
+
+    def __init__(self, query_ids, rows, info):
+        self.query_ids, self.rows, self.info = query_ids, rows, info
+
+
+def solve_distributed(local_xyz, first_id: int, n_total: int, k: int, group=None, halo: int | None = None,
+                      density: float = 3.1, keep_rows: bool = True) -> SlabRows:
+    """One pass of the multi-GPU hot path on this rank's chunk (CUDA tensor [n_local, 3])."""
+    import torch
+    import torch.distributed as dist
+    import cuda_knearests_b200 as K
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    D, zsplit = grid_and_split(n_total, world, density)
+    halo = halo_planes(k, density) if halo is None else halo
+    info = {"grid_dim": D, "zsplit": zsplit, "attempts": 0}
+    while True:
+        info["attempts"] += 1
+        info["halo"] = halo
+        send_xyz, send_ids, counts = route_device(local_xyz, first_id, D, zsplit, halo)
+        recv_xyz, recv_ids, recv_counts = exchange(send_xyz, send_ids, counts, group)
+        del send_xyz, send_ids
+        zb, ze, ozb, oze = held_planes(zsplit, rank, halo, D)
+        ok = 1
+        rows = qids = None
+        info.update(points_held=int(recv_xyz.shape[0]), sent=int(sum(counts)), planes=(zb, ze, ozb, oze))
+        if oze > ozb and recv_xyz.shape[0] > 0:
+            p = K.KnProblem(recv_xyz, k=k, grid_dim=D, slab=(zb, ze, ozb, oze), density=density)
+            try:
+                p.solve()
+                info.update(p.timings(), queries=p.info.query_count)
+                if keep_rows:
+                    nq = p.info.query_count
+                    rows = torch.empty((nq, k), dtype=torch.int32, device=recv_xyz.device)
+                    qids = torch.empty((nq,), dtype=torch.int32, device=recv_xyz.device)
+                    torch.cuda.current_stream().synchronize()
+                    K._check(K.lib().knc_get_knearests_global(p._h, C.c_void_p(recv_ids.data_ptr()),
+                                                              C.c_void_p(rows.data_ptr()), C.c_void_p(qids.data_ptr())))
+            except K.KnError as e:
+                if e.code != 5:  # KNC_ERR_HALO
+                    raise
+                ok = 0
+            finally:
+                p.free()
+        flag = torch.tensor([ok], dtype=torch.int32, device=local_xyz.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        if int(flag.item()) == 1:
+            return SlabRows(qids, rows, info)
+        halo += 2  # some query reached beyond its halo: widen everywhere and repeat (never silently wrong)
+
+
+# ------------------------------------------------------------------------------------------- bench
+def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_config, ClockSampler, measured_peak_gbs):
+    """bench.py for N > 1: 100 M points cut into z-slabs, strong scaling.  A step is the whole multi-GPU
+    hot path: route + NCCL all-to-all + kn_prepare (slab) + kn_solve + rows to global ids."""
+    import json
+    import torch
+    import torch.distributed as dist
+    import cuda_knearests_b200 as K
+    dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    dev = torch.device("cuda", local_rank)
+    n, k = args.n, args.k
+    lo, hi = (rank * n) // world, ((rank + 1) * n) // world
+    pts = K.generate_uniform_device(hi - lo, seed=SEED, first=lo, device=dev)
+
+    def step():
+        return solve_distributed(pts, lo, n, k, density=args.density or 3.1)
+
+    for _ in range(args.warmup):
+        res = step()
+    dist.barrier()
+    torch.cuda.synchronize()
+    infos = []
+    with ClockSampler(local_rank) as clk:
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            res = step()
+            infos.append(res.info)
+        torch.cuda.synchronize()
+        dist.barrier()
+        wall = time.perf_counter() - t0
+    t = torch.tensor([wall], dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    wall = float(t.item())
+    stats = torch.tensor([infos[-1].get("solve_ms", 0.0), infos[-1].get("build_ms", 0.0),
+                          float(infos[-1].get("queries", 0)), float(infos[-1]["points_held"]),
+                          float(infos[-1]["sent"])], dtype=torch.float64, device=dev)
+    allstats = [torch.empty_like(stats) for _ in range(world)]
+    dist.all_gather(allstats, stats)
+
+    e2e = None
+    if not args.no_e2e:
+        host_in = torch.empty((hi - lo, 3), dtype=torch.float32, pin_memory=True)
+        host_in.copy_(pts)
+        nq_max = int(max(s[2].item() for s in allstats))
+        host_rows = torch.empty((nq_max + 1024, k), dtype=torch.int32, pin_memory=True)
+        host_qid = torch.empty((nq_max + 1024,), dtype=torch.int32, pin_memory=True)
+
+        def step_e2e():
+            d_in = host_in.to(dev, non_blocking=True)
+            r = solve_distributed(d_in, lo, n, k, density=args.density or 3.1)
+            nq = r.rows.shape[0]
+            host_rows[:nq].copy_(r.rows, non_blocking=True)
+            host_qid[:nq].copy_(r.query_ids, non_blocking=True)
+            torch.cuda.synchronize()
+
+        step_e2e()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e_steps = max(2, min(args.steps, 3))
+        t0 = time.perf_counter()
+        for _ in range(e_steps):
+            step_e2e()
+        dist.barrier()
+        te = torch.tensor([(time.perf_counter() - t0) / e_steps], dtype=torch.float64, device=dev)
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e = {"value": n / float(te.item()), "unit": UNIT, "h2d_bytes_per_step": 12 * n,
+               "d2h_bytes_per_step": 4 * k * n + 4 * n, "ms_per_step": 1e3 * float(te.item()), "steps": e_steps,
+               "call": "per rank: pinned host chunk -> device, route + all-to-all + knc_prepare_ex(slab) + knc_solve + "
+                       "knc_get_knearests_global, rows and query ids -> pinned host"}
+
+    if rank == 0:
+        peak, peak_kind = measured_peak_gbs()
+        solve_ms = max(float(s[0].item()) for s in allstats)
+        queries = [int(s[2].item()) for s in allstats]
+        worst = max(range(world), key=lambda r: float(allstats[r][0].item()))
+        achieved = (12 + 4 * k) * queries[worst] / (float(allstats[worst][0].item()) * 1e-3) / 1e9
+        cfg = workload_config(args)
+        cfg.update(parallelism=f"z-slabs x{world}", halo_planes=infos[-1]["halo"], grid_dim=infos[-1]["grid_dim"],
+                   points_held_per_rank=[int(s[3].item()) for s in allstats],
+                   records_sent_per_rank=[int(s[4].item()) for s in allstats],
+                   exchange="NCCL all_to_all_single of (xyz, id) records, inside the timed step")
+        line = {"metric": METRIC, "value": n / (wall / args.steps), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True,
+                "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+                "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 12 * args.steps * world,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": None, "kernel": "kn_query_fast_kernel (slowest rank)",
+                             "kernel_ms": float(allstats[worst][0].item()),
+                             "algorithmic_bytes": (12 + 4 * k) * queries[worst],
+                             "peak_kind": f"{peak_kind} copy bandwidth (burst), per GPU"},
+                "cpu_baseline": None,
+                "device_ms": {"query_max_over_ranks": solve_ms,
+                              "grid_build_max_over_ranks": max(float(s[1].item()) for s in allstats)},
+                "queries_per_rank": queries, "halo_attempts": infos[-1]["attempts"]}
+        print(json.dumps(line), flush=True)
+    dist.barrier()
+    dist.destroy_process_group()

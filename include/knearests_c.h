@@ -144,6 +144,27 @@ const char *knc_version(void);
  * (the reference has no generator); bit-identical to oracle/knn_oracle.c:kno_generate_uniform. */
 int knc_generate_uniform_device(float *d_xyz, long long first, long long count, uint64_t seed);
 
+/* ---- multi-GPU, one process per GPU ---------------------------------------------------
+ * No reference counterpart: the reference is single-GPU.  The cloud is cut into z-slabs of
+ * cell planes of one GLOBAL grid: rank d owns planes [zsplit[d], zsplit[d+1]) and additionally needs the
+ * `halo` planes on either side.  The caller exchanges the buffers (NCCL all-to-all); these two calls are
+ * the device work before and after.
+ *
+ * knc_slab_route: stable multi-split of n local points (DEVICE xyz, global ids first_id .. first_id+n-1)
+ * into per-destination groups: d_out_xyz / d_out_id (DEVICE, room for `capacity` records) receive, for
+ * d = 0..nranks-1 in turn, every point whose plane lies in [zsplit[d]-halo, zsplit[d+1]+halo), in input
+ * order; out_counts[d] (HOST) is the size of group d.  zsplit is a HOST array of nranks+1 planes rising
+ * from 0 to grid_dim.  KNC_ERR_NOMEM if the groups do not fit `capacity` (out_counts is still filled). */
+int knc_slab_route(const float *d_xyz, int n, unsigned int first_id, int grid_dim, int nranks, const int *zsplit,
+                   int halo, float *d_out_xyz, unsigned int *d_out_id, long long capacity, long long *out_counts);
+
+/* Rows of a solved (slab) handle in GLOBAL ids: d_ids[i] (DEVICE) is the global id of the handle's i-th
+ * input point; d_out_rows (DEVICE, query_count*k) gets ids[perm[knn]], d_out_query_ids (DEVICE,
+ * query_count, may be NULL) the global id of each row's query.  (The reference's index remap,
+ * test_knearests.cu:155-160, extended by the global id table.) */
+int knc_get_knearests_global(knc_problem *p, const unsigned int *d_ids, unsigned int *d_out_rows,
+                             unsigned int *d_out_query_ids);
+
 /* ---- for callers that must not allocate --------------------------------------------------------
  * No counterpart in the reference (its every entry point cudaMallocs, knearests.cu:205-231).
  * The grid build's exclusive scan on its own: d_ptrs[c] = sum of d_counters[0..c), d_ptrs[cells] =

@@ -1,0 +1,67 @@
+"""Multi-GPU path on ONE GPU: the ranks are emulated one after the other (route every rank's chunk with
+knc_slab_route, hand each destination its groups in rank order -- what the all-to-all delivers -- then
+slab prepare + solve + rows in global ids).  The rows must be the single-GPU rows, bit for bit.
+The NCCL exchange itself is exercised by `bench.py --gpus N` under torchrun and, on the CPU, by
+tests/test_multi_gpu_logic.py."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from test_multi_gpu_logic import numpy_route
+
+pytestmark = pytest.mark.gpu
+
+
+def test_route_kernel_is_the_stable_multisplit(kn, oracle):
+    import torch
+    from cuda_knearests_b200 import slabs
+    n, world = 300_000, 4
+    pts = oracle.generate_uniform(n, seed=31)
+    D, zsplit = slabs.grid_and_split(1_200_000, world)
+    dev = torch.from_numpy(pts).cuda()
+    for halo in (0, 3, 40):
+        sx, si, counts = slabs.route_device(dev, 5_000_000, D, zsplit, halo)
+        wx, wi, wc = numpy_route(pts, 5_000_000, D, zsplit, halo)
+        assert counts == wc
+        tot = sum(counts)
+        assert np.array_equal(si[:tot].cpu().numpy(), wi) and np.array_equal(sx[:tot].cpu().numpy(), wx)
+
+
+@pytest.mark.parametrize("world,k,n", [(2, 20, 400_000), (4, 8, 600_000), (8, 20, 1_000_000), (3, 50, 300_000)])
+def test_emulated_ranks_reproduce_single_gpu_rows(kn, oracle, world, k, n):
+    import torch
+    from cuda_knearests_b200 import slabs
+    pts = oracle.generate_uniform(n, seed=20171004)
+    # single GPU, rows in original ids
+    with kn.KnProblem(pts, k=k) as p:
+        p.solve()
+        want = p.get_knearests_original()
+    D, zsplit = slabs.grid_and_split(n, world)
+    halo = slabs.halo_planes(k)
+    dev = torch.from_numpy(pts).cuda()
+    routed = []
+    for r in range(world):
+        lo, hi = r * n // world, (r + 1) * n // world
+        sx, si, counts = slabs.route_device(dev[lo:hi].contiguous(), lo, D, zsplit, halo)
+        routed.append((sx, si, np.concatenate([[0], np.cumsum(counts)])))
+    got = np.full((n, k), 0xFFFFFFFF, np.uint32)
+    seen = np.zeros(n, bool)
+    for d in range(world):
+        rx = torch.cat([sx[off[d]:off[d + 1]] for sx, _, off in routed]).contiguous()
+        ri = torch.cat([si[off[d]:off[d + 1]] for _, si, off in routed]).contiguous()
+        zb, ze, ozb, oze = slabs.held_planes(zsplit, d, halo, D)
+        with kn.KnProblem(rx, k=k, grid_dim=D, slab=(zb, ze, ozb, oze)) as p:
+            p.solve()
+            nq = p.info.query_count
+            rows = torch.empty((nq, k), dtype=torch.int32, device="cuda")
+            qid = torch.empty((nq,), dtype=torch.int32, device="cuda")
+            torch.cuda.synchronize()
+            kn._check(kn.lib().knc_get_knearests_global(p._h, C.c_void_p(ri.data_ptr()), C.c_void_p(rows.data_ptr()),
+                                                        C.c_void_p(qid.data_ptr())))
+        q = qid.cpu().numpy()
+        assert not seen[q].any()
+        seen[q] = True
+        got[q] = rows.cpu().numpy().view(np.uint32)
+    assert seen.all()                      # every point is a query of exactly one rank
+    assert np.array_equal(got, want)       # and its row is the single-GPU row
