@@ -25,7 +25,7 @@ MAX_K = 256
 
 # every symbol include/knearests_c.h declares (tests check that the library exports all of them)
 C_ABI_SYMBOLS = [
-    "knc_prepare", "knc_prepare_ex", "knc_solve", "knc_free", "knc_get_points", "knc_get_permutation",
+    "knc_prepare", "knc_prepare_ex", "knc_solve", "knc_solve_to_host", "knc_free", "knc_get_points", "knc_get_permutation",
     "knc_get_knearests", "knc_get_knearests_original", "knc_get_stats", "knc_get_info", "knc_get_timings",
     "knc_grid_dim", "knc_last_error", "knc_version", "knc_generate_uniform_device", "knc_scan_cells_noalloc",
     "knc_slab_route", "knc_get_knearests_global",
@@ -94,6 +94,7 @@ def lib() -> C.CDLL:
             getattr(L, nm).argtypes = [vp]
         for nm in ("knc_get_points", "knc_get_permutation", "knc_get_knearests", "knc_get_knearests_original"):
             getattr(L, nm).argtypes = [vp, vp]
+        L.knc_solve_to_host.argtypes = [vp, vp, C.c_int]
         L.knc_get_stats.argtypes = [vp, C.POINTER(Stats)]
         L.knc_get_info.argtypes = [vp, C.POINTER(Info)]
         L.knc_get_timings.argtypes = [vp, C.POINTER(Timings)]
@@ -164,6 +165,14 @@ class KnProblem:
         _check(lib().knc_solve(self._h))
         self.info = self._info()
         return self
+
+    def solve_to_host(self, out: np.ndarray | None = None, chunks: int = 8) -> np.ndarray:
+        """kn_solve + kn_get_knearests overlapped (knc_solve_to_host); `out` should be page-locked."""
+        if out is None:
+            out = np.empty((self.info.query_count, self.info.k), np.uint32)
+        _check(lib().knc_solve_to_host(self._h, out.ctypes.data, int(chunks)))
+        self.info = self._info()
+        return out
 
     def get_points(self) -> np.ndarray:  # kn_get_points, knearests.cu:410
         out = np.empty((self.info.n, 3), np.float32)

@@ -83,6 +83,7 @@ void free_device_state(knc_problem *p) {
         cudaStreamSynchronize(st);
         cudaStreamDestroy(st);
     }
+    if (p->copy_stream) cudaStreamDestroy(p->copy_stream);
     for (cudaEvent_t &e : p->ev)
         if (e) cudaEventDestroy(e);
 }
@@ -231,9 +232,11 @@ int knc_prepare(const float *xyz, int n, int k, knc_problem **out) {
     return knc_prepare_ex(xyz, n, &o, out);
 }
 
-int knc_solve(knc_problem *p) {
+// The query, optionally streamed to the host: the query range is cut into `chunks` pieces; the rows of
+// piece c travel device->host on a second stream while piece c+1 is being computed.
+static int solve_impl(knc_problem *p, unsigned int *out_knn_host, int chunks, const char *who) {
     int rc = KNC_OK;
-    if (!p) return fail(KNC_ERR_INVALID, "knc_solve: NULL handle");
+    if (!p) return fail(KNC_ERR_INVALID, "%s: NULL handle", who);
     cudaStream_t st = p->stream;
     GridGeom g;
     const int D = p->dim_global;
@@ -246,17 +249,38 @@ int knc_solve(knc_problem *p) {
     unsigned diag[4] = {0, 0, 0, 0};
     int *d_retry = NULL;  // scratch of the solve: queries the fast kernel hands to the general kernel
     const int force_general = p->algorithm == 1;
-    CU(dev_alloc((void **)&d_retry, sizeof(int) * (size_t)(p->query_count > 0 ? p->query_count : 1), st));
+    if (chunks < 1 || !out_knn_host) chunks = 1;
+    if (chunks > 64) chunks = 64;
+    const int per = (p->query_count + chunks - 1) / chunks;
+    cudaEvent_t done[64];
+    int made = 0;
+    CU(dev_alloc((void **)&d_retry, sizeof(int) * (size_t)(per > 0 ? per : 1), st));
+    if (out_knn_host && !p->copy_stream) CU(cudaStreamCreateWithFlags(&p->copy_stream, cudaStreamNonBlocking));
     CU(cudaMemsetAsync(p->d_diag, 0, sizeof(unsigned) * 4, st));
     CU(cudaEventRecord(p->ev[2], st));
-    CU(kn_launch_query(p->d_points4, p->pub.d_ptrs, g, p->pub.allocated_points, p->k, p->query_begin,
-                       p->query_count, (float)(r0 * r0), p->pub.d_knearests, p->d_diag, d_retry, force_general, st));
+    for (int c = 0; c < chunks; ++c) {
+        const int q0 = c * per, qn = (p->query_count - q0) < per ? (p->query_count - q0) : per;
+        if (qn <= 0) break;
+        unsigned int *rows = p->pub.d_knearests + (size_t)q0 * p->k;
+        if (c) CU(cudaMemsetAsync(p->d_diag + 3, 0, sizeof(unsigned), st));  // the retry list starts empty
+        CU(kn_launch_query(p->d_points4, p->pub.d_ptrs, g, p->pub.allocated_points, p->k, p->query_begin + q0, qn,
+                           (float)(r0 * r0), rows, p->d_diag, d_retry, force_general, st));
+        if (out_knn_host) {
+            CU(cudaEventCreateWithFlags(&done[made], cudaEventDisableTiming));
+            ++made;
+            CU(cudaEventRecord(done[made - 1], st));
+            CU(cudaStreamWaitEvent(p->copy_stream, done[made - 1], 0));
+            CU(cudaMemcpyAsync(out_knn_host + (size_t)q0 * p->k, rows, sizeof(unsigned) * (size_t)qn * p->k,
+                               cudaMemcpyDeviceToHost, p->copy_stream));
+        }
+    }
     CU(cudaEventRecord(p->ev[3], st));
     CU(cudaMemcpyAsync(diag, p->d_diag, sizeof(diag), cudaMemcpyDeviceToHost, st));
     CU(cudaMemcpyAsync(p->pub.d_cell_max, p->d_diag + 1, sizeof(float), cudaMemcpyDeviceToDevice, st));
     CU(cudaStreamSynchronize(st));  // blocking, like knearests.cu:373
+    if (out_knn_host) CU(cudaStreamSynchronize(p->copy_stream));
     CU(cudaEventElapsedTime(&p->t.solve_ms, p->ev[2], p->ev[3]));
-    p->t.restarts = diag[0] + diag[3];  // restarts inside the general kernel + queries retried after the fast one
+    p->t.restarts = diag[0];  // restarts inside the general kernel + queries it took over from the fast one
     memcpy(&p->t.max_radius2, &diag[1], sizeof(float));
     p->solved = 1;
     if (verbose()) {
@@ -265,11 +289,19 @@ int knc_solve(knc_problem *p) {
                 sqrt((double)p->t.max_radius2) / g.w, r0 / g.w, diag[0], p->query_count);
     }
     if (diag[2])
-        rc = fail(KNC_ERR_HALO, "knc_solve: %u queries reach beyond the halo planes [%d,%d) of this slab", diag[2],
+        rc = fail(KNC_ERR_HALO, "%s: %u queries reach beyond the halo planes [%d,%d) of this slab", who, diag[2],
                   p->z_begin, p->z_end);
 out:
+    for (int i = 0; i < made; ++i) cudaEventDestroy(done[i]);
     if (d_retry) cudaFreeAsync(d_retry, st);
     return rc;
+}
+
+int knc_solve(knc_problem *p) { return solve_impl(p, NULL, 1, "knc_solve"); }
+
+int knc_solve_to_host(knc_problem *p, unsigned int *out_knn, int chunks) {
+    if (!out_knn) return fail(KNC_ERR_INVALID, "knc_solve_to_host: out_knn is NULL");
+    return solve_impl(p, out_knn, chunks > 0 ? chunks : 8, "knc_solve_to_host");
 }
 
 int knc_free(knc_problem *p) {

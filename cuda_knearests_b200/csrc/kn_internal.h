@@ -24,6 +24,7 @@ struct knc_problem {
     float4 *d_points4;           // [n] x, y, z, bits(original index): what the query kernel reads
     unsigned int *d_diag;        // [4] restarts, max radius^2 bits, halo misses, spare
     cudaStream_t stream;
+    cudaStream_t copy_stream;    // device->host row copies of knc_solve_to_host (created on first use)
     cudaEvent_t ev[4];
     knc_timings t;
 };

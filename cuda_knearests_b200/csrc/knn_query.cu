@@ -351,6 +351,7 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
     unsigned long long *L = smem + tid;
     const long long total = RETRY ? (long long)*P.retry_count : (long long)P.query_count;
     const long long stride = (long long)gridDim.x * QB;
+    if (RETRY && blockIdx.x == 0 && tid == 0 && total) atomicAdd(P.diag + 0, (unsigned)total);  // counted as restarts
 
     for (long long row0 = (long long)blockIdx.x * QB; row0 < total; row0 += stride) {
         const bool valid = row0 + tid < total;

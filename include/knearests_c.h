@@ -107,6 +107,13 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
  * May be called again; it recomputes the same rows. */
 int knc_solve(knc_problem *p);
 
+/* knc_solve and kn_get_knearests in one call, overlapped: the query runs in `chunks` pieces (<= 0: 8) and
+ * the rows of each finished piece are copied to out_knn (HOST, query_count*k unsigned; page-locked
+ * memory is needed for the copy to overlap) while the next piece is computed.  The rows also stay on the
+ * device.  Replaces the pair kn_solve + kn_get_knearests (knearests.cu:348,430) for callers whose result
+ * must end up on the host: the 4*k*n-byte read-back otherwise costs more than the query itself. */
+int knc_solve_to_host(knc_problem *p, unsigned int *out_knn, int chunks);
+
 /* Replaces kn_free (knearests.h:23, knearests.cu:396-408).  NULL is accepted. */
 int knc_free(knc_problem *p);
 

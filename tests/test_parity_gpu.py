@@ -115,6 +115,20 @@ def test_solve_is_idempotent_and_deterministic(kn, oracle):
     assert np.array_equal(a, b) and np.array_equal(a, c)
 
 
+def test_solve_to_host_streams_the_same_rows(kn, oracle):
+    import torch
+    pts = oracle.generate_uniform(333_333, seed=9)
+    want = run_engine(kn, pts, 20)["knn"]
+    for chunks in (1, 3, 8, 64):
+        pinned = torch.empty(want.shape, dtype=torch.int32, pin_memory=True)
+        with kn.KnProblem(pts, k=20) as p:
+            got = p.solve_to_host(pinned.numpy().view(np.uint32), chunks=chunks)
+            assert np.array_equal(got, want)
+            assert np.array_equal(p.get_knearests(), want)  # rows also stay on the device
+    with kn.KnProblem(pts, k=20) as p:
+        assert np.array_equal(p.solve_to_host(), want)      # pageable buffer: same result, no overlap
+
+
 def test_original_space_remap(kn, oracle):
     pts = oracle.generate_uniform(60_000, seed=4)
     with kn.KnProblem(pts, k=8) as p:
