@@ -53,7 +53,10 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=16_000_000, help="points of the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--density", type=float, default=0.0)
+    ap.add_argument("--density", type=float, default=1.0,
+                    help="points per grid cell handed to knc_prepare_ex (library default: the reference's 3.1; "
+                         "1.0 is ~14 %% faster on B200, profiles/r1_notes.md)")
+    ap.add_argument("--no-ref-gpu", action="store_true", help="skip timing the reference's own knearests.cu on this GPU")
     return ap.parse_args()
 
 
@@ -156,6 +159,7 @@ def main_reference(args, rank: int):
 def workload_config(args, n_sample_note=None):
     c = {"workload": f"synthetic uniform {args.n} points in [0,1000)^3 (splitmix64 counter generator, seed {SEED}), "
                      f"k={args.k}: kn_prepare + kn_solve", "n_points": args.n, "k": args.k,
+         "grid_density": args.density,
          "l2_policy": "inputs larger than L2 (points 12 B x n, rows 4k B x n >> 126 MB); no flush needed"}
     if n_sample_note:
         c["cpu_sample_points"] = n_sample_note
@@ -255,13 +259,33 @@ def main_ours(args, rank: int, world: int, local_rank: int):
         cb = cpu_reference_run(min(args.cpu_sample, n), k)
         cpu_baseline = {kk: cb[kk] for kk in ("value", "unit", "cores", "kind", "sample")}
 
+    # ---- the reference's OWN GPU kernel (knearests.cu, unmodified, compiled for sm_100a: oracle/_ref) on
+    # the same cloud and the same GPU, timed around its blocking kn_prepare / kn_solve (informational)
+    reference_gpu = None
+    if not args.no_ref_gpu:
+        try:
+            import oracle as O
+            if O.have_ref(f"libref_knearests_k{k}.so"):
+                host_pts = pts.cpu().numpy()
+                del pts
+                torch.cuda.empty_cache()
+                ref = O.RefGpu(k)
+                ref.run(host_pts[: min(n, 1_000_000)], fetch=False)  # context / module warm-up
+                r = ref.run(host_pts, fetch=False)
+                reference_gpu = {"kernel": "knearests.cu (reference, sm_100a build)", "n_points": n, "k": k,
+                                 "kn_solve_ms": 1e3 * r["solve_s"], "kn_prepare_ms_incl_h2d": 1e3 * r["prepare_s"],
+                                 "solve_only_value": n / r["solve_s"], "unit": UNIT,
+                                 "ours_over_reference_solve": (1e3 * r["solve_s"]) / solve_ms}
+        except Exception as e:  # informational only
+            reference_gpu = {"unavailable": str(e)[:200]}
+
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args),
             "clocks": clk.summary(), "e2e": e2e, "gpu_launches": KERNELS_PER_STEP * args.steps,
             "roofline": roofline, "cpu_baseline": cpu_baseline,
             "device_ms": {"grid_build": build_ms, "query": solve_ms},
-            "solve_only_value": n / (solve_ms * 1e-3),
+            "solve_only_value": n / (solve_ms * 1e-3), "reference_gpu": reference_gpu,
             "restarts": int(timings[-1]["restarts"])}
     print(json.dumps(line), flush=True)
 

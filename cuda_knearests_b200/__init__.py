@@ -19,7 +19,7 @@ from pathlib import Path
 import numpy as np
 
 HERE = Path(__file__).resolve().parent
-LIB_PATH = HERE / "libknearests_b200.so"
+LIB_PATH = Path(os.environ.get("KN_LIB_PATH", HERE / "libknearests_b200.so"))  # override: A/B builds
 EMPTY = 0xFFFFFFFF
 MAX_K = 256
 

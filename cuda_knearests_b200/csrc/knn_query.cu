@@ -47,6 +47,11 @@
 #include <stdint.h>
 
 #include "kn_internal.h"
+#include "sort_network.h"
+
+#ifndef KN_QSLOTS
+#define KN_QSLOTS 8
+#endif
 
 namespace {
 
@@ -166,10 +171,14 @@ __device__ __forceinline__ void report_diag(const QueryParams &P, const QueryGeo
 }
 
 // ======================================================================================== fast path
-constexpr int kFirstBatch = 9;   // the own row and its 8 neighbours (lower bound 0)
-constexpr int kNextBatch = 8;    // rows per later batch
-constexpr int kSpanSlots = 9;    // spans a lane can hold per batch
-constexpr int kQueueSlots = 8;   // pending candidates per lane between insertion bursts
+#ifndef KN_FIRST_BATCH
+#define KN_FIRST_BATCH 9
+#define KN_NEXT_BATCH 8
+#endif
+constexpr int kFirstBatch = KN_FIRST_BATCH;  // rows of the first batch: the own row and its 8 neighbours (lower bound 0)
+constexpr int kNextBatch = KN_NEXT_BATCH;    // rows per later batch
+constexpr int kSpanSlots = KN_FIRST_BATCH > KN_NEXT_BATCH ? KN_FIRST_BATCH : KN_NEXT_BATCH;  // spans held per batch
+constexpr int kQueueSlots = KN_QSLOTS;   // pending candidates per lane between insertion bursts
 constexpr int kChunk = 4;        // candidates a lane takes per lock-step iteration
 
 __device__ __forceinline__ void cswap(unsigned long long &a, unsigned long long &b) {
@@ -225,24 +234,34 @@ __global__ void __launch_bounds__(QB) kn_query_fast_kernel(const __grid_constant
                     if (key < kth) { b[u] = key; ++nb; }
                 }
             }
-            cswap(b[0], b[1]); cswap(b[2], b[3]); cswap(b[4], b[5]); cswap(b[6], b[7]);
-            cswap(b[0], b[2]); cswap(b[1], b[3]); cswap(b[4], b[6]); cswap(b[5], b[7]);
-            cswap(b[1], b[2]); cswap(b[5], b[6]); cswap(b[0], b[4]); cswap(b[3], b[7]);
-            cswap(b[1], b[5]); cswap(b[2], b[6]);
-            cswap(b[1], b[4]); cswap(b[3], b[6]);
-            cswap(b[2], b[4]); cswap(b[3], b[5]);
-            cswap(b[3], b[4]);
+#define KN_CE(i, j) cswap(b[i], b[j]);
+#if KN_QSLOTS == 16
+            KN_SORT_NETWORK_16(KN_CE)
+#else
+            KN_SORT_NETWORK_8(KN_CE)
+#endif
+#undef KN_CE
 #pragma unroll
             for (int u = 0; u < kQueueSlots; ++u) QU[u * QB] = b[u];
+            // Merge from the back; entries that fall beyond slot K-1 are dropped.  Branch-free body: the
+            // side that was consumed is reloaded through ONE predicated load from a selected address,
+            // so the lanes of a burst never split (0 = "exhausted" sentinel, smaller than any live key
+            // that could still have to move).
             int i = cnt - 1, j = nb - 1, o = cnt + nb - 1;
             unsigned long long e = i >= 0 ? L[i * QB] : 0ull;
             unsigned long long bj = j >= 0 ? QU[j * QB] : 0ull;
-            while (j >= 0) {  // merge from the back; entries that fall beyond slot K-1 are dropped
-                const bool from_list = i >= 0 && e > bj;
+            while (j >= 0) {
+                const bool from_list = e > bj;
                 if (o < K) L[o * QB] = from_list ? e : bj;
-                if (from_list) { --i; e = i >= 0 ? L[i * QB] : 0ull; }
-                else { --j; bj = j >= 0 ? QU[j * QB] : 0ull; }
+                i -= from_list ? 1 : 0;
+                j -= from_list ? 0 : 1;
                 --o;
+                const int idx = from_list ? i : j;
+                const unsigned long long *src = from_list ? L + i * QB : QU + j * QB;
+                unsigned long long val = 0ull;
+                if (idx >= 0) val = *src;
+                e = from_list ? val : e;
+                bj = from_list ? bj : val;
             }
             cnt = min(K, cnt + nb);
             if (cnt == K) kth = L[(K - 1) * QB];
