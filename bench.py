@@ -56,6 +56,7 @@ def parse():
     ap.add_argument("--density", type=float, default=1.0,
                     help="points per grid cell handed to knc_prepare_ex (library default: the reference's 3.1; "
                          "1.0 is ~14 %% faster on B200, profiles/r1_notes.md)")
+    ap.add_argument("--algorithm", type=int, default=0, help="knc_options.algorithm (0 auto, 1 general, 2 insertion kernel)")
     ap.add_argument("--no-ref-gpu", action="store_true", help="skip timing the reference's own knearests.cu on this GPU")
     return ap.parse_args()
 
@@ -187,7 +188,7 @@ def main_ours(args, rank: int, world: int, local_rank: int):
     torch.cuda.synchronize()
 
     def step_device():
-        p = K.KnProblem(pts, k=k, density=args.density)
+        p = K.KnProblem(pts, k=k, density=args.density, algorithm=args.algorithm)
         p.solve()
         t = p.timings()
         p.free()
@@ -236,7 +237,7 @@ def main_ours(args, rank: int, world: int, local_rank: int):
         import ctypes as C
 
         def step_e2e():
-            p = K.KnProblem(host_in_np, k=k, density=args.density)   # kn_prepare: H2D + grid build
+            p = K.KnProblem(host_in_np, k=k, density=args.density, algorithm=args.algorithm)   # kn_prepare: H2D + grid build
             p.solve_to_host(rows_np, chunks=8)                        # kn_solve + kn_get_knearests, overlapped
             K._check(K.lib().knc_get_permutation(p._h, perm_np.ctypes.data))    # kn_get_permutation
             p.free()

@@ -248,7 +248,7 @@ static int solve_impl(knc_problem *p, unsigned int *out_knn_host, int chunks, co
     const double r0 = cbrt(3.0 * lambda / (4.0 * M_PI * rho)) * p->search_scale;
     unsigned diag[4] = {0, 0, 0, 0};
     int *d_retry = NULL;  // scratch of the solve: queries the fast kernel hands to the general kernel
-    const int force_general = p->algorithm == 1;
+    const int force_general = p->algorithm;  // 0 auto, 1 general kernel only, 2 insertion kernel for every k
     if (chunks < 1 || !out_knn_host) chunks = 1;
     if (chunks > 64) chunks = 64;
     const int per = (p->query_count + chunks - 1) / chunks;

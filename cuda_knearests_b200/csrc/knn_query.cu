@@ -76,6 +76,7 @@ struct QueryParams {
     GridGeom g;
     int n, k, query_begin, query_count;
     float radius0_sq;
+    int use_select;        // small k: remember-then-select kernel instead of the insertion kernel
     int *retry_list;       // sorted positions of the queries the fast kernel could not finish
     unsigned int *retry_count;
     RowTable tab;
@@ -356,6 +357,135 @@ __global__ void __launch_bounds__(QB) kn_query_fast_kernel(const __grid_constant
     }
 }
 
+// ===================================================================================== select path
+// For small compile-time k (8, 20).  Nothing is kept sorted while scanning: every candidate inside the
+// first-guess sphere is only REMEMBERED (its 32-bit position, appended to a per-lane buffer in shared
+// memory; no k-th distance, no insertion bursts, fully warp-uniform row loop because the bound never
+// changes).  When the sphere has been searched, the scan state is dead and each lane rebuilds the keys of
+// its buffered candidates (the points are still in L1/L2), sorts 32 of them at a time with a fixed
+// Batcher network in registers -- branch-free, all lanes busy -- and keeps the k smallest.
+// k <= count <= capacity  =>  the row is exact (the whole sphere was searched and holds >= k points);
+// anything else goes to the retry list of the general kernel.
+constexpr int kSelectCap = 48;   // buffered candidates per lane (32-bit positions)
+constexpr int kSelectNet = 32;   // keys sorted per round
+
+template <int K_T, int QB>
+__global__ void __launch_bounds__(QB, 6) kn_query_select_kernel(const __grid_constant__ QueryParams P) {
+    static_assert(K_T > 0 && K_T <= kSelectNet - 8, "select path: k must leave room for new keys in a round");
+    extern __shared__ unsigned long long smem[];
+    const int tid = threadIdx.x;
+    unsigned int *BUF = reinterpret_cast<unsigned int *>(smem) + tid;                                   // [kSelectCap][QB]
+    int2 *SP = reinterpret_cast<int2 *>(reinterpret_cast<unsigned int *>(smem) + kSelectCap * QB) + tid;  // [kSpanSlots][QB]
+    const int D = P.g.D, zb = P.g.zb, ze = P.g.ze;
+    const float w = P.g.w, invw = P.g.invw;
+    const long long row0 = (long long)blockIdx.x * QB;
+    const bool valid = row0 + tid < P.query_count;
+    const int q = P.query_begin + (int)min(row0 + tid, (long long)P.query_count - 1);
+    const QueryGeom s = query_geom(__ldg(P.pts + q), P.g);
+    const float r2 = P.radius0_sq;
+    int cnt = 0;            // candidates seen inside the sphere (may exceed the capacity: then the query is retried)
+
+    // ---- search the sphere: rows in batches, spans first, then a lock-step stream over them -----------------
+    for (int e0 = 0, e1 = min(kFirstBatch, P.tab.n); e0 < P.tab.n && P.tab.lb2[e0] <= r2;
+         e0 = e1, e1 = min(e0 + kNextBatch, P.tab.n)) {
+        int nsp = 0;
+        for (int e = e0; e < e1; e += 4) {
+            int alo[4], ahi[4];
+            bool ok[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                ok[u] = false;
+                const int ee = e + u;
+                if (ee < e1 && valid && P.tab.lb2[ee] <= r2) {
+                    const int dj = P.tab.dj[ee], dk = P.tab.dk[ee];
+                    const int j = s.cj + dj, k = s.ck + dk;
+                    if (j >= 0 && j < D && k >= zb && k < ze) {
+                        const float lbyz2 = row_lower_bound2(s, dj, dk, w);
+                        if (lbyz2 <= r2) {
+                            int ilo, ihi;
+                            row_x_range(s, r2, lbyz2, invw, D, ilo, ihi);
+                            const int row = ((k - zb) * D + j) * D;
+                            alo[u] = row + ilo;
+                            ahi[u] = row + ihi + 1;
+                            ok[u] = ilo <= ihi;
+                        }
+                    }
+                }
+            }
+            int b4[4], e4[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) { b4[u] = __ldg(P.ptrs + alo[u]); e4[u] = __ldg(P.ptrs + ahi[u]); }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u] && b4[u] < e4[u]) { SP[nsp * QB] = make_int2(b4[u], e4[u]); ++nsp; }
+        }
+        int sp = 0, p = 0, end = 0;
+        if (nsp > 0) { const int2 t = SP[0]; p = t.x; end = t.y; sp = 1; }
+        while (__any_sync(0xffffffffu, p < end)) {
+            float4 c[kChunk];
+#pragma unroll
+            for (int u = 0; u < kChunk; ++u) {
+                c[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (p + u < end) c[u] = __ldg(P.pts + p + u);
+            }
+            // branch-free body: the arithmetic runs for all four slots, only the append is predicated
+#pragma unroll
+            for (int u = 0; u < kChunk; ++u) {
+                const float dx = c[u].x - s.px, dy = c[u].y - s.py, dz = c[u].z - s.pz;
+                const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+                const bool pass = (p + u < end) & (d2 <= r2) & (p + u != q);  // self excluded, knearests.cu:123
+                if (pass) BUF[min(cnt, kSelectCap - 1) * QB] = (unsigned)(p + u);  // beyond the capacity: retried anyway
+                cnt += pass ? 1 : 0;
+            }
+            asm volatile("" ::"f"(c[0].w), "f"(c[1].w), "f"(c[2].w), "f"(c[3].w));  // keep .w allocated (see above)
+            p += kChunk;
+            if (p >= end && sp < nsp) { const int2 t = SP[sp * QB]; p = t.x; end = t.y; ++sp; }
+        }
+    }
+
+    // ---- select: rebuild keys, sort 32 at a time, keep the K_T smallest ------------------------------------------
+    const bool finished = valid && cnt >= K_T && cnt <= kSelectCap;
+    if (valid && !finished) P.retry_list[atomicAdd(P.retry_count, 1u)] = q;
+    const int have = finished ? cnt : 0;
+    unsigned long long a[kSelectNet];
+    for (int base = 0, round = 0; round == 0 || __any_sync(0xffffffffu, have > base); ++round) {
+        if (round == 0) {
+#pragma unroll
+            for (int u = 0; u < kSelectNet; ++u) {
+                a[u] = ~0ull;
+                if (u < have) { const int pos = (int)BUF[u * QB]; a[u] = make_key(__ldg(P.pts + pos), s, pos); }
+            }
+            base = kSelectNet;
+        } else {  // the K_T best so far stay in a[0..K_T), the other slots take the next candidates
+#pragma unroll
+            for (int u = K_T; u < kSelectNet; ++u) {
+                const int idx = base + (u - K_T);
+                a[u] = ~0ull;
+                if (idx < have) { const int pos = (int)BUF[idx * QB]; a[u] = make_key(__ldg(P.pts + pos), s, pos); }
+            }
+            base += kSelectNet - K_T;
+        }
+#define KN_CE(i, j) cswap(a[i], a[j]);
+        KN_SORT_NETWORK_32(KN_CE)
+#undef KN_CE
+    }
+    report_diag(P, s, finished, finished ? __uint_as_float((unsigned)(a[K_T - 1] >> 32)) : 0.f, 0u, tid);
+
+    // ---- coalesced row output (through the buffer area, now free) -----------------------------------------------
+    __syncthreads();
+    unsigned int *OUT = reinterpret_cast<unsigned int *>(smem);
+#pragma unroll
+    for (int u = 0; u < K_T; ++u) OUT[u * QB + tid] = (unsigned)a[u];
+    __syncthreads();
+    const int rows = (int)min((long long)QB, (long long)P.query_count - row0);
+    unsigned int *out = P.knn + row0 * K_T;
+    for (int idx = tid; idx < rows * K_T; idx += QB) {
+        const int t = idx / K_T, sl = idx - t * K_T;
+        out[idx] = OUT[sl * QB + t];
+    }
+}
+
 // ===================================================================================== general path
 // Per-lane nested loops over rows and candidates, restarts with a growing radius, plain square rings
 // of rows beyond the table: exact for any input.  RETRY = false: one thread per query of the range
@@ -472,7 +602,19 @@ cudaError_t launch(const QueryParams &P, bool fast, cudaStream_t st) {
     const size_t list_bytes = sizeof(unsigned long long) * (size_t)P.k * QB;
     const unsigned blocks = (unsigned)(((long long)P.query_count + QB - 1) / QB);
     cudaError_t e;
-    if (fast) {
+    if (fast && (K_T == 8 || K_T == 20) && P.use_select) {
+        if constexpr (K_T == 8 || K_T == 20) {
+            const size_t smem = (sizeof(unsigned) * kSelectCap + sizeof(int2) * kSpanSlots) * QB;
+            e = cudaFuncSetAttribute(kn_query_select_kernel<K_T, QB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+            if (e != cudaSuccess) return e;
+            kn_query_select_kernel<K_T, QB><<<blocks, QB, smem, st>>>(P);
+        }
+        e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)list_bytes);
+        if (e != cudaSuccess) return e;
+        const unsigned retry_blocks = blocks < 148u * 8u ? blocks : 148u * 8u;
+        kn_query_general_kernel<K_T, QB, true><<<retry_blocks, QB, list_bytes, st>>>(P);
+    } else if (fast) {
         const size_t smem = list_bytes + sizeof(unsigned long long) * (size_t)(kSpanSlots + kQueueSlots) * QB;
         e = cudaFuncSetAttribute(kn_query_fast_kernel<K_T, QB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
@@ -531,12 +673,13 @@ cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const Gr
     P.n = n; P.k = k; P.query_begin = query_begin; P.query_count = query_count;
     P.radius0_sq = radius0_sq;
     P.retry_list = d_retry_list;
+    P.use_select = force_general != 2;  // algorithm 2 = insertion kernel even for small k (A/B, tests)
     P.retry_count = d_diag + 3;
     fill_table(P.tab, g.w);
     // The fast kernel searches table rows only: usable when every row outside the table is provably
     // farther than the first-guess radius.
     const float beyond = fmaxf(0.f, (float)kTableRing * g.w - kMargin);
-    const bool fast = !force_general && d_retry_list && radius0_sq < beyond * beyond * kShrink;
+    const bool fast = force_general != 1 && d_retry_list && radius0_sq < beyond * beyond * kShrink;
     switch (k) {
         case 8: return launch<8, 128>(P, fast, st);
         case 20: return launch<20, 128>(P, fast, st);
