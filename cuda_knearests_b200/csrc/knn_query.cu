@@ -320,12 +320,13 @@ __global__ void __launch_bounds__(QB) kn_query_fast_kernel(const __grid_constant
                 c[u] = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (p + u < end) c[u] = __ldg(P.pts + p + u);
             }
+            // branch-free body: the arithmetic runs for all four slots, only the append is predicated
 #pragma unroll
             for (int u = 0; u < kChunk; ++u) {
-                if (p + u < end) {
-                    const unsigned long long key = make_key(c[u], s, p + u);
-                    if (key < kth && p + u != q) { QU[qlen * QB] = key; ++qlen; }  // self excluded, knearests.cu:123
-                }
+                const unsigned long long key = make_key(c[u], s, p + u);
+                const bool pass = (p + u < end) & (key < kth) & (p + u != q);  // self excluded, knearests.cu:123
+                if (pass) QU[qlen * QB] = key;
+                qlen += pass ? 1 : 0;
             }
             // the unused .w lanes stay allocated until here: otherwise they are recycled at once and the
             // next instruction that writes them waits for the loads (seen in profiles/r1_query_v2*)
@@ -368,6 +369,10 @@ __global__ void __launch_bounds__(QB) kn_query_fast_kernel(const __grid_constant
 // anything else goes to the retry list of the general kernel.
 constexpr int kSelectCap = 48;   // buffered candidates per lane (32-bit positions)
 constexpr int kSelectNet = 32;   // keys sorted per round
+#ifndef KN_SEL_CHUNK
+#define KN_SEL_CHUNK 4
+#endif
+constexpr int kSelChunk = KN_SEL_CHUNK;  // candidates a lane takes per lock-step iteration
 
 template <int K_T, int QB>
 __global__ void __launch_bounds__(QB, 6) kn_query_select_kernel(const __grid_constant__ QueryParams P) {
@@ -423,23 +428,24 @@ __global__ void __launch_bounds__(QB, 6) kn_query_select_kernel(const __grid_con
         int sp = 0, p = 0, end = 0;
         if (nsp > 0) { const int2 t = SP[0]; p = t.x; end = t.y; sp = 1; }
         while (__any_sync(0xffffffffu, p < end)) {
-            float4 c[kChunk];
+            float4 c[kSelChunk];
 #pragma unroll
-            for (int u = 0; u < kChunk; ++u) {
+            for (int u = 0; u < kSelChunk; ++u) {
                 c[u] = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (p + u < end) c[u] = __ldg(P.pts + p + u);
             }
             // branch-free body: the arithmetic runs for all four slots, only the append is predicated
 #pragma unroll
-            for (int u = 0; u < kChunk; ++u) {
+            for (int u = 0; u < kSelChunk; ++u) {
                 const float dx = c[u].x - s.px, dy = c[u].y - s.py, dz = c[u].z - s.pz;
                 const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
                 const bool pass = (p + u < end) & (d2 <= r2) & (p + u != q);  // self excluded, knearests.cu:123
                 if (pass) BUF[min(cnt, kSelectCap - 1) * QB] = (unsigned)(p + u);  // beyond the capacity: retried anyway
                 cnt += pass ? 1 : 0;
             }
-            asm volatile("" ::"f"(c[0].w), "f"(c[1].w), "f"(c[2].w), "f"(c[3].w));  // keep .w allocated (see above)
-            p += kChunk;
+            #pragma unroll
+            for (int u = 0; u < kSelChunk; ++u) asm volatile("" ::"f"(c[u].w));  // keep .w allocated (see above)
+            p += kSelChunk;
             if (p >= end && sp < nsp) { const int2 t = SP[sp * QB]; p = t.x; end = t.y; ++sp; }
         }
     }
