@@ -375,8 +375,8 @@ constexpr int kSelectNet = 32;   // keys sorted per round
 constexpr int kSelChunk = KN_SEL_CHUNK;  // candidates a lane takes per lock-step iteration
 
 template <int K_T, int QB>
-__global__ void __launch_bounds__(QB, 6) kn_query_select_kernel(const __grid_constant__ QueryParams P) {
-    static_assert(K_T > 0 && K_T <= kSelectNet - 8, "select path: k must leave room for new keys in a round");
+__global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_constant__ QueryParams P) {
+    static_assert(K_T > 0 && K_T + 1 <= kSelectNet - 8, "select path: k must leave room for new keys in a round");
     extern __shared__ unsigned long long smem[];
     const int tid = threadIdx.x;
     unsigned int *BUF = reinterpret_cast<unsigned int *>(smem) + tid;                                   // [kSelectCap][QB]
@@ -450,39 +450,58 @@ __global__ void __launch_bounds__(QB, 6) kn_query_select_kernel(const __grid_con
         }
     }
 
-    // ---- select: rebuild keys, sort 32 at a time, keep the K_T smallest ------------------------------------------
-    const bool finished = valid && cnt >= K_T && cnt <= kSelectCap;
-    if (valid && !finished) P.retry_list[atomicAdd(P.retry_count, 1u)] = q;
-    const int have = finished ? cnt : 0;
-    unsigned long long a[kSelectNet];
+    // ---- select ------------------------------------------------------------------------------------------
+    // Rebuild each buffered candidate's d2 (its record is still in L1/L2) and sort 32-BIT keys
+    //     (bits(d2) with the low 6 bits replaced by the buffer slot)
+    // 32 at a time with the Batcher network: a compare-exchange is one integer min and one max, the keys
+    // take 32 registers (64-bit keys took 64 and cost the scan its occupancy).  The 6 dropped mantissa bits
+    // can only matter when two of the k+1 smallest truncated distances coincide; that is checked (k adjacent
+    // compares) and such a query is retried exactly by the general kernel -- about 0.5 % on uniform clouds,
+    // every query on a lattice.  Otherwise ascending truncated keys ARE ascending (d2, position).
+    static_assert(kSelectCap <= 64, "slot must fit the 6 low key bits");
+    const bool searched = valid && cnt >= K_T && cnt <= kSelectCap;
+    const int have = searched ? cnt : 0;
+    unsigned a[kSelectNet];
     for (int base = 0, round = 0; round == 0 || __any_sync(0xffffffffu, have > base); ++round) {
-        if (round == 0) {
+        // Later rounds keep the K_T + 1 smallest so far: the extra one guards the border -- whatever is
+        // dropped has a key >= a[K_T], so if a[K_T-1] and a[K_T] differ in their truncated distance at
+        // the end, nothing that was dropped could have belonged to the row.
+        const int lo = round == 0 ? 0 : K_T + 1;
 #pragma unroll
-            for (int u = 0; u < kSelectNet; ++u) {
-                a[u] = ~0ull;
-                if (u < have) { const int pos = (int)BUF[u * QB]; a[u] = make_key(__ldg(P.pts + pos), s, pos); }
+        for (int u = 0; u < kSelectNet; ++u) {
+            if (u >= lo) {
+                const int slot = base + (u - lo);
+                a[u] = 0xFFFFFFFFu;
+                if (slot < have) {
+                    const int pos = (int)BUF[slot * QB];
+                    a[u] = ((unsigned)(make_key(__ldg(P.pts + pos), s, pos) >> 32) & ~63u) | (unsigned)slot;
+                }
             }
-            base = kSelectNet;
-        } else {  // the K_T best so far stay in a[0..K_T), the other slots take the next candidates
-#pragma unroll
-            for (int u = K_T; u < kSelectNet; ++u) {
-                const int idx = base + (u - K_T);
-                a[u] = ~0ull;
-                if (idx < have) { const int pos = (int)BUF[idx * QB]; a[u] = make_key(__ldg(P.pts + pos), s, pos); }
-            }
-            base += kSelectNet - K_T;
         }
-#define KN_CE(i, j) cswap(a[i], a[j]);
+        base += kSelectNet - lo;
+#define KN_CE(i, j)                                     \
+    {                                                   \
+        const unsigned lo_ = min(a[i], a[j]);           \
+        a[j] = max(a[i], a[j]);                         \
+        a[i] = lo_;                                     \
+    }
         KN_SORT_NETWORK_32(KN_CE)
 #undef KN_CE
     }
-    report_diag(P, s, finished, finished ? __uint_as_float((unsigned)(a[K_T - 1] >> 32)) : 0.f, 0u, tid);
+    bool exact = searched;
+#pragma unroll
+    for (int u = 0; u < K_T; ++u) exact = exact && (a[u] >> 6) < (a[u + 1] >> 6);  // a[K_T] exists: K_T < kSelectNet
+    if (valid && !exact) P.retry_list[atomicAdd(P.retry_count, 1u)] = q;
+    report_diag(P, s, exact, exact ? __uint_as_float((a[K_T - 1] | 63u)) : 0.f, 0u, tid);
 
-    // ---- coalesced row output (through the buffer area, now free) -----------------------------------------------
+    // ---- coalesced row output (through the buffer area: read all k positions, then overwrite) -----------------
+    unsigned res[K_T];
+#pragma unroll
+    for (int u = 0; u < K_T; ++u) res[u] = exact ? BUF[(a[u] & 63u) * QB] : KNC_EMPTY;
     __syncthreads();
     unsigned int *OUT = reinterpret_cast<unsigned int *>(smem);
 #pragma unroll
-    for (int u = 0; u < K_T; ++u) OUT[u * QB + tid] = (unsigned)a[u];
+    for (int u = 0; u < K_T; ++u) OUT[u * QB + tid] = res[u];
     __syncthreads();
     const int rows = (int)min((long long)QB, (long long)P.query_count - row0);
     unsigned int *out = P.knn + row0 * K_T;

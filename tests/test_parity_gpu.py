@@ -212,6 +212,19 @@ def test_planar_and_lattice_clouds_with_many_ties(kn, oracle):
     assert np.array_equal(r["knn"], g.knn_exact(8))
 
 
+@pytest.mark.parametrize("bits", [7, 9, 11, 13])
+def test_quantised_coordinates_many_ties_and_near_ties(kn, oracle, bits):
+    """Coordinates on a 2^bits lattice: squared distances collide exactly or differ in their last bits
+    everywhere, including at the k/k+1 border and across the select kernel's sorting rounds -- the cases
+    in which a truncated-key comparison must hand the query to the exact path."""
+    raw = oracle.generate_uniform(200_000, seed=40 + bits)
+    pts = (np.floor(raw / 1000.0 * 2 ** bits) * (1000.0 / 2 ** bits)).astype(np.float32)
+    for K in (8, 20):
+        r = run_engine(kn, pts, K)
+        g = assert_layout_equals_oracle(oracle, pts, r)
+        assert np.array_equal(r["knn"], g.knn_exact(K))
+
+
 def test_slab_mode_rows_equal_whole_grid_rows(kn, oracle):
     """z-slab handles: planes [zb,ze) held, queries for [ozb,oze) only; the rows are the
     whole-grid rows, shifted by the slab's first sorted position."""
