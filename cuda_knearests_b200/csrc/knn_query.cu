@@ -425,28 +425,47 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
             for (int u = 0; u < 4; ++u)
                 if (ok[u] && b4[u] < e4[u]) { SP[nsp * QB] = make_int2(b4[u], e4[u]); ++nsp; }
         }
+        // Lock-step stream over the lane's spans, kSelChunk candidates per iteration, software-pipelined:
+        // the records of the NEXT chunk are requested before the current one is evaluated (two register
+        // buffers used in turn; the scan is bound by load latency at this occupancy).
         int sp = 0, p = 0, end = 0;
         if (nsp > 0) { const int2 t = SP[0]; p = t.x; end = t.y; sp = 1; }
-        while (__any_sync(0xffffffffu, p < end)) {
-            float4 c[kSelChunk];
+        auto fetch = [&](float4(&c)[kSelChunk], int at, int stop) {
 #pragma unroll
             for (int u = 0; u < kSelChunk; ++u) {
                 c[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (p + u < end) c[u] = __ldg(P.pts + p + u);
+                if (at + u < stop) c[u] = __ldg(P.pts + at + u);
             }
-            // branch-free body: the arithmetic runs for all four slots, only the append is predicated
+        };
+        auto evaluate = [&](float4(&c)[kSelChunk], int at, int stop) {  // branch-free: only the append is predicated
 #pragma unroll
             for (int u = 0; u < kSelChunk; ++u) {
                 const float dx = c[u].x - s.px, dy = c[u].y - s.py, dz = c[u].z - s.pz;
                 const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
-                const bool pass = (p + u < end) & (d2 <= r2) & (p + u != q);  // self excluded, knearests.cu:123
-                if (pass) BUF[min(cnt, kSelectCap - 1) * QB] = (unsigned)(p + u);  // beyond the capacity: retried anyway
+                const bool pass = (at + u < stop) & (d2 <= r2) & (at + u != q);  // self excluded, knearests.cu:123
+                if (pass) BUF[min(cnt, kSelectCap - 1) * QB] = (unsigned)(at + u);  // beyond the capacity: retried anyway
                 cnt += pass ? 1 : 0;
             }
-            #pragma unroll
+#pragma unroll
             for (int u = 0; u < kSelChunk; ++u) asm volatile("" ::"f"(c[u].w));  // keep .w allocated (see above)
-            p += kSelChunk;
-            if (p >= end && sp < nsp) { const int2 t = SP[sp * QB]; p = t.x; end = t.y; ++sp; }
+        };
+        auto next_chunk = [&](int &pn, int &endn, int &spn) {
+            pn = p + kSelChunk; endn = end; spn = sp;
+            if (pn >= end && sp < nsp) { const int2 t = SP[sp * QB]; pn = t.x; endn = t.y; spn = sp + 1; }
+        };
+        float4 ca[kSelChunk], cb[kSelChunk];
+        fetch(ca, p, end);
+        while (__any_sync(0xffffffffu, p < end)) {
+            int pn, endn, spn;
+            next_chunk(pn, endn, spn);
+            fetch(cb, pn, endn);
+            evaluate(ca, p, end);
+            p = pn; end = endn; sp = spn;
+            if (!__any_sync(0xffffffffu, p < end)) break;
+            next_chunk(pn, endn, spn);
+            fetch(ca, pn, endn);
+            evaluate(cb, p, end);
+            p = pn; end = endn; sp = spn;
         }
     }
 
