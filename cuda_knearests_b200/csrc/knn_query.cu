@@ -367,16 +367,20 @@ __global__ void __launch_bounds__(QB) kn_query_fast_kernel(const __grid_constant
 // Batcher network in registers -- branch-free, all lanes busy -- and keeps the k smallest.
 // k <= count <= capacity  =>  the row is exact (the whole sphere was searched and holds >= k points);
 // anything else goes to the retry list of the general kernel.
-constexpr int kSelectCap = 48;   // buffered candidates per lane (32-bit positions)
-constexpr int kSelectNet = 32;   // keys sorted per round
+// NET keys are sorted per round, CAP candidates can be buffered per lane (32-bit positions):
+//   k <= 20 : NET 32, CAP 48      k <= 50 : NET 64, CAP 96
 #ifndef KN_SEL_CHUNK
 #define KN_SEL_CHUNK 4
 #endif
 constexpr int kSelChunk = KN_SEL_CHUNK;  // candidates a lane takes per lock-step iteration
 
-template <int K_T, int QB>
+template <int K_T, int QB, int NET, int CAP>
 __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_constant__ QueryParams P) {
-    static_assert(K_T > 0 && K_T + 1 <= kSelectNet - 8, "select path: k must leave room for new keys in a round");
+    static_assert(K_T > 0 && K_T + 1 <= NET - 8, "select path: k must leave room for new keys in a round");
+    static_assert(NET == 32 || NET == 64, "select path: networks exist for 32 and 64 keys");
+    constexpr int kSelectCap = CAP, kSelectNet = NET;
+    constexpr unsigned kSlotMask = CAP <= 64 ? 63u : 127u;  // low key bits that hold the buffer slot
+    constexpr int kSlotBits = CAP <= 64 ? 6 : 7;
     extern __shared__ unsigned long long smem[];
     const int tid = threadIdx.x;
     unsigned int *BUF = reinterpret_cast<unsigned int *>(smem) + tid;                                   // [kSelectCap][QB]
@@ -471,13 +475,13 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
 
     // ---- select ------------------------------------------------------------------------------------------
     // Rebuild each buffered candidate's d2 (its record is still in L1/L2) and sort 32-BIT keys
-    //     (bits(d2) with the low 6 bits replaced by the buffer slot)
+    //     (bits(d2) with the low 6 or 7 bits replaced by the buffer slot)
     // 32 at a time with the Batcher network: a compare-exchange is one integer min and one max, the keys
     // take 32 registers (64-bit keys took 64 and cost the scan its occupancy).  The 6 dropped mantissa bits
     // can only matter when two of the k+1 smallest truncated distances coincide; that is checked (k adjacent
     // compares) and such a query is retried exactly by the general kernel -- about 0.5 % on uniform clouds,
     // every query on a lattice.  Otherwise ascending truncated keys ARE ascending (d2, position).
-    static_assert(kSelectCap <= 64, "slot must fit the 6 low key bits");
+    static_assert(kSelectCap <= 128, "slot must fit the low key bits");
     const bool searched = valid && cnt >= K_T && cnt <= kSelectCap;
     const int have = searched ? cnt : 0;
     unsigned a[kSelectNet];
@@ -493,7 +497,7 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
                 a[u] = 0xFFFFFFFFu;
                 if (slot < have) {
                     const int pos = (int)BUF[slot * QB];
-                    a[u] = ((unsigned)(make_key(__ldg(P.pts + pos), s, pos) >> 32) & ~63u) | (unsigned)slot;
+                    a[u] = ((unsigned)(make_key(__ldg(P.pts + pos), s, pos) >> 32) & ~kSlotMask) | (unsigned)slot;
                 }
             }
         }
@@ -504,19 +508,19 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
         a[j] = max(a[i], a[j]);                         \
         a[i] = lo_;                                     \
     }
-        KN_SORT_NETWORK_32(KN_CE)
+        if constexpr (NET == 32) { KN_SORT_NETWORK_32(KN_CE) } else { KN_SORT_NETWORK_64(KN_CE) }
 #undef KN_CE
     }
     bool exact = searched;
 #pragma unroll
-    for (int u = 0; u < K_T; ++u) exact = exact && (a[u] >> 6) < (a[u + 1] >> 6);  // a[K_T] exists: K_T < kSelectNet
+    for (int u = 0; u < K_T; ++u) exact = exact && (a[u] >> kSlotBits) < (a[u + 1] >> kSlotBits);  // a[K_T] exists: K_T < NET
     if (valid && !exact) P.retry_list[atomicAdd(P.retry_count, 1u)] = q;
-    report_diag(P, s, exact, exact ? __uint_as_float((a[K_T - 1] | 63u)) : 0.f, 0u, tid);
+    report_diag(P, s, exact, exact ? __uint_as_float((a[K_T - 1] | kSlotMask)) : 0.f, 0u, tid);
 
     // ---- coalesced row output (through the buffer area: read all k positions, then overwrite) -----------------
     unsigned res[K_T];
 #pragma unroll
-    for (int u = 0; u < K_T; ++u) res[u] = exact ? BUF[(a[u] & 63u) * QB] : KNC_EMPTY;
+    for (int u = 0; u < K_T; ++u) res[u] = exact ? BUF[(a[u] & kSlotMask) * QB] : KNC_EMPTY;
     __syncthreads();
     unsigned int *OUT = reinterpret_cast<unsigned int *>(smem);
 #pragma unroll
@@ -646,12 +650,15 @@ cudaError_t launch(const QueryParams &P, bool fast, cudaStream_t st) {
     const size_t list_bytes = sizeof(unsigned long long) * (size_t)P.k * QB;
     const unsigned blocks = (unsigned)(((long long)P.query_count + QB - 1) / QB);
     cudaError_t e;
-    if (fast && (K_T == 8 || K_T == 20) && P.use_select) {
-        if constexpr (K_T == 8 || K_T == 20) {
-            const size_t smem = (sizeof(unsigned) * kSelectCap + sizeof(int2) * kSpanSlots) * QB;
-            e = cudaFuncSetAttribute(kn_query_select_kernel<K_T, QB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    constexpr bool kHasSelect = K_T == 8 || K_T == 20 || K_T == 32 || K_T == 50;
+    if (fast && kHasSelect && P.use_select) {
+        if constexpr (kHasSelect) {
+            constexpr int NET = K_T <= 20 ? 32 : 64, CAP = K_T <= 20 ? 48 : 96;
+            const size_t smem = (sizeof(unsigned) * CAP + sizeof(int2) * kSpanSlots) * QB;
+            e = cudaFuncSetAttribute(kn_query_select_kernel<K_T, QB, NET, CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     (int)smem);
             if (e != cudaSuccess) return e;
-            kn_query_select_kernel<K_T, QB><<<blocks, QB, smem, st>>>(P);
+            kn_query_select_kernel<K_T, QB, NET, CAP><<<blocks, QB, smem, st>>>(P);
         }
         e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)list_bytes);
