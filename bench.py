@@ -220,7 +220,7 @@ def main_ours(args, rank: int, world: int, local_rank: int):
         except Exception:
             traffic = None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": "kn_query_fast_kernel (+ retry kernel)", "kernel_ms": solve_ms,
+                "traffic": traffic, "kernel": "kn_query_select_kernel (+ retry kernel)", "kernel_ms": solve_ms,
                 "algorithmic_bytes": algo_bytes, "peak_kind": f"{peak_kind} copy bandwidth (burst)"}
 
     # ---- end to end: host buffers in, host buffers out, through the reference-facing call ----------

@@ -344,7 +344,7 @@ __global__ void __launch_bounds__(QB) kn_query_fast_kernel(const __grid_constant
 
     // fewer than k points inside the first-guess sphere: hand the query to the general kernel
     const bool finished = valid && cnt == K;
-    if (valid && !finished) P.retry_list[atomicAdd(P.retry_count, 1u)] = q;
+    if (valid && !finished) P.retry_list[atomicAdd(P.retry_count, 1u)] = q | (int)0x80000000;  // needs a larger sphere
     report_diag(P, s, finished, finished ? __uint_as_float((unsigned)(kth >> 32)) : 0.f, 0u, tid);
 
     // ---- coalesced row output --------------------------------------------------------------------
@@ -514,7 +514,9 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
     bool exact = searched;
 #pragma unroll
     for (int u = 0; u < K_T; ++u) exact = exact && (a[u] >> kSlotBits) < (a[u + 1] >> kSlotBits);  // a[K_T] exists: K_T < NET
-    if (valid && !exact) P.retry_list[atomicAdd(P.retry_count, 1u)] = q;
+    // bit 31 of a retry entry: the sphere held fewer than k points, so the retry must search a larger one
+    // (an overflowing buffer or a truncated-key tie is retried with the same radius)
+    if (valid && !exact) P.retry_list[atomicAdd(P.retry_count, 1u)] = q | (cnt < K_T ? (int)0x80000000 : 0);
     report_diag(P, s, exact, exact ? __uint_as_float((a[K_T - 1] | kSlotMask)) : 0.f, 0u, tid);
 
     // ---- coalesced row output (through the buffer area: read all k positions, then overwrite) -----------------
@@ -553,12 +555,13 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
     for (long long row0 = (long long)blockIdx.x * QB; row0 < total; row0 += stride) {
         const bool valid = row0 + tid < total;
         const long long slot = min(row0 + tid, total - 1);
-        const int q = RETRY ? P.retry_list[slot] : P.query_begin + (int)slot;
+        const int entry = RETRY ? P.retry_list[slot] : P.query_begin + (int)slot;
+        const int q = entry & 0x7FFFFFFF;
         const QueryGeom s = query_geom(__ldg(P.pts + q), P.g);
 
         int cnt = 0;
         unsigned long long kth = ~0ull;
-        float r2 = RETRY ? P.radius0_sq * 2.25f : P.radius0_sq;
+        float r2 = (RETRY && entry < 0) ? P.radius0_sq * 2.25f : P.radius0_sq;
         float bound2 = r2;
         bool pruned = false;
         unsigned restarts = 0;

@@ -227,7 +227,7 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
                 "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 12 * args.steps * world,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": None, "kernel": "kn_query_fast_kernel (slowest rank)",
+                             "traffic": None, "kernel": "kn_query_select_kernel (slowest rank)",
                              "kernel_ms": float(allstats[worst][0].item()),
                              "algorithmic_bytes": (12 + 4 * k) * queries[worst],
                              "peak_kind": f"{peak_kind} copy bandwidth (burst), per GPU"},
