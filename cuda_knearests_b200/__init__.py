@@ -28,7 +28,7 @@ C_ABI_SYMBOLS = [
     "knc_prepare", "knc_prepare_ex", "knc_solve", "knc_solve_to_host", "knc_free", "knc_get_points", "knc_get_permutation",
     "knc_get_knearests", "knc_get_knearests_original", "knc_get_stats", "knc_get_info", "knc_get_timings",
     "knc_grid_dim", "knc_last_error", "knc_version", "knc_generate_uniform_device", "knc_scan_cells_noalloc",
-    "knc_slab_route", "knc_get_knearests_global",
+    "knc_slab_route", "knc_get_knearests_global", "knc_set_index_offset", "knc_get_permutation_global",
 ]
 # the reference's own (C++-mangled) entry points, knearests.h:21-29
 CXX_ABI_SYMBOLS = [
@@ -104,6 +104,8 @@ def lib() -> C.CDLL:
         L.knc_slab_route.argtypes = [vp, C.c_int, C.c_uint, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, vp, vp,
                                      C.c_longlong, C.POINTER(C.c_longlong)]
         L.knc_get_knearests_global.argtypes = [vp, vp, vp, vp]
+        L.knc_set_index_offset.argtypes = [vp, C.c_longlong]
+        L.knc_get_permutation_global.argtypes = [vp, vp, vp]
         L.knc_last_error.restype = C.c_char_p
         L.knc_version.restype = C.c_char_p
         _lib = L

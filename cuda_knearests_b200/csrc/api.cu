@@ -264,7 +264,7 @@ static int solve_impl(knc_problem *p, unsigned int *out_knn_host, int chunks, co
         unsigned int *rows = p->pub.d_knearests + (size_t)q0 * p->k;
         if (c) CU(cudaMemsetAsync(p->d_diag + 3, 0, sizeof(unsigned), st));  // the retry list starts empty
         CU(kn_launch_query(p->d_points4, p->pub.d_ptrs, g, p->pub.allocated_points, p->k, p->query_begin + q0, qn,
-                           (float)(r0 * r0), rows, p->d_diag, d_retry, force_general, st));
+                           (float)(r0 * r0), rows, p->d_diag, d_retry, force_general, p->index_offset, st));
         if (out_knn_host) {
             CU(cudaEventCreateWithFlags(&done[made], cudaEventDisableTiming));
             ++made;
@@ -302,6 +302,15 @@ int knc_solve(knc_problem *p) { return solve_impl(p, NULL, 1, "knc_solve"); }
 int knc_solve_to_host(knc_problem *p, unsigned int *out_knn, int chunks) {
     if (!out_knn) return fail(KNC_ERR_INVALID, "knc_solve_to_host: out_knn is NULL");
     return solve_impl(p, out_knn, chunks > 0 ? chunks : 8, "knc_solve_to_host");
+}
+
+int knc_set_index_offset(knc_problem *p, long long offset) {
+    if (!p) return fail(KNC_ERR_INVALID, "knc_set_index_offset: NULL handle");
+    if (offset < 0 || offset + p->pub.allocated_points > 0xFFFFFFFEll)
+        return fail(KNC_ERR_INVALID, "knc_set_index_offset: %lld + %d points does not fit 32-bit indices", offset,
+                    p->pub.allocated_points);
+    p->index_offset = (unsigned)offset;
+    return KNC_OK;
 }
 
 int knc_free(knc_problem *p) {

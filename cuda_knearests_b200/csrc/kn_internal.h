@@ -15,6 +15,7 @@ struct knc_problem {
     float density;
     float search_scale;
     int algorithm;               // knc_options.algorithm
+    unsigned int index_offset;   // knc_set_index_offset: added to every stored neighbour index
     int z_begin, z_end;          // cell planes held (z_end - z_begin == pub.dimz planes LOCALLY)
     int own_z_begin, own_z_end;
     int dim_global;              // global cubic resolution D (pub.dimx == pub.dimy == D)
@@ -58,7 +59,8 @@ cudaError_t kn_launch_remap_original(const unsigned int *d_knn, const unsigned i
 // ---- knn_query.cu ------------------------------------------------------------------------------
 cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const GridGeom &g, int n, int k,
                             int query_begin, int query_count, float radius0_sq, unsigned int *d_knn,
-                            unsigned int *d_diag, int *d_retry_list, int force_general, cudaStream_t st);
+                            unsigned int *d_diag, int *d_retry_list, int force_general, unsigned int index_offset,
+                            cudaStream_t st);
 
 // ---- api.cu ------------------------------------------------------------------------------------
 int kn_set_error(int code, const char *fmt, ...);  // records the message knc_last_error() returns

@@ -77,6 +77,7 @@ struct QueryParams {
     int n, k, query_begin, query_count;
     float radius0_sq;
     int use_select;        // small k: remember-then-select kernel instead of the insertion kernel
+    unsigned index_offset; // added to every stored neighbour index (slab mode: local -> global sorted position)
     int *retry_list;       // sorted positions of the queries the fast kernel could not finish
     unsigned int *retry_count;
     RowTable tab;
@@ -354,7 +355,8 @@ __global__ void __launch_bounds__(QB) kn_query_fast_kernel(const __grid_constant
     unsigned int *out = P.knn + row0 * K;
     for (int idx = tid; idx < rows * K; idx += QB) {
         const int t = idx / K, sl = idx - t * K;
-        out[idx] = (unsigned)smem[sl * QB + t];
+        const unsigned v = (unsigned)smem[sl * QB + t];
+        out[idx] = v == KNC_EMPTY ? v : v + P.index_offset;
     }
 }
 
@@ -522,7 +524,7 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
     // ---- coalesced row output (through the buffer area: read all k positions, then overwrite) -----------------
     unsigned res[K_T];
 #pragma unroll
-    for (int u = 0; u < K_T; ++u) res[u] = exact ? BUF[(a[u] & kSlotMask) * QB] : KNC_EMPTY;
+    for (int u = 0; u < K_T; ++u) res[u] = exact ? BUF[(a[u] & kSlotMask) * QB] + P.index_offset : KNC_EMPTY;
     __syncthreads();
     unsigned int *OUT = reinterpret_cast<unsigned int *>(smem);
 #pragma unroll
@@ -633,7 +635,10 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
         if (RETRY) {  // scattered rows: each thread writes its own
             if (valid) {
                 unsigned int *out = P.knn + (long long)(q - P.query_begin) * K;
-                for (int t = 0; t < K; ++t) out[t] = (unsigned)L[t * QB];
+                for (int t = 0; t < K; ++t) {
+                    const unsigned v = (unsigned)L[t * QB];
+                    out[t] = v == KNC_EMPTY ? v : v + P.index_offset;
+                }
             }
         } else {      // contiguous rows: one coalesced run per block
             __syncthreads();
@@ -641,7 +646,8 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
             unsigned int *out = P.knn + row0 * K;
             for (int idx = tid; idx < rows * K; idx += QB) {
                 const int t = idx / K, sl = idx - t * K;
-                out[idx] = (unsigned)smem[sl * QB + t];
+                const unsigned v = (unsigned)smem[sl * QB + t];
+                out[idx] = v == KNC_EMPTY ? v : v + P.index_offset;
             }
             __syncthreads();
         }
@@ -720,13 +726,15 @@ void fill_table(RowTable &t, float w) {
 
 cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const GridGeom &g, int n, int k,
                             int query_begin, int query_count, float radius0_sq, unsigned int *d_knn,
-                            unsigned int *d_diag, int *d_retry_list, int force_general, cudaStream_t st) {
+                            unsigned int *d_diag, int *d_retry_list, int force_general, unsigned int index_offset,
+                            cudaStream_t st) {
     if (query_count <= 0) return cudaSuccess;
     QueryParams P;
     P.pts = d_points4; P.ptrs = d_ptrs; P.knn = d_knn; P.diag = d_diag; P.g = g;
     P.n = n; P.k = k; P.query_begin = query_begin; P.query_count = query_count;
     P.radius0_sq = radius0_sq;
     P.retry_list = d_retry_list;
+    P.index_offset = index_offset;
     P.use_select = force_general != 2;  // algorithm 2 = insertion kernel even for small k (A/B, tests)
     P.retry_count = d_diag + 3;
     fill_table(P.tab, g.w);

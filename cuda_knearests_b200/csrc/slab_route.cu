@@ -130,7 +130,26 @@ __global__ void kn_rows_to_global_kernel(const unsigned *__restrict__ knn, const
     if (out_query_ids && e - r * k == 0) out_query_ids[r] = __ldg(ids + __ldg(perm + query_begin + r));
 }
 
+// out[i] = ids[perm[query_begin + i]]: this rank's slice of the global permutation
+__global__ void kn_perm_to_global_kernel(const unsigned *__restrict__ perm, const unsigned *__restrict__ ids,
+                                         int query_begin, int count, unsigned *__restrict__ out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < count) out[i] = __ldg(ids + __ldg(perm + query_begin + i));
+}
+
 }  // namespace
+
+extern "C" int knc_get_permutation_global(knc_problem *p, const unsigned int *d_ids, unsigned int *d_out) {
+    if (!p || !d_ids || !d_out) return kn_set_error(KNC_ERR_INVALID, "knc_get_permutation_global: NULL argument");
+    if (p->query_count > 0) {
+        kn_perm_to_global_kernel<<<(unsigned)((p->query_count + 255) / 256), 256, 0, p->stream>>>(
+            p->pub.d_permutation, d_ids, p->query_begin, p->query_count, d_out);
+        cudaError_t e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+        if (e != cudaSuccess) return kn_set_error(KNC_ERR_CUDA, "knc_get_permutation_global: %s", cudaGetErrorString(e));
+    }
+    return KNC_OK;
+}
 
 extern "C" int knc_slab_route(const float *d_xyz, int n, unsigned int first_id, int grid_dim, int nranks,
                               const int *zsplit, int halo, float *d_out_xyz, unsigned int *d_out_id,

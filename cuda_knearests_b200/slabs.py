@@ -90,15 +90,34 @@ def route_device(local_xyz, first_id: int, D: int, zsplit, halo: int):
 
 
 class SlabRows:
-    """Result of one rank: rows of GLOBAL ids for the queries this rank owns."""
+    """Result of one rank, in the single-GPU contract made global:
+      rows        view of the handle's d_knearests: [query_count, k] GLOBAL sorted positions (torch, device)
+      permutation [query_count] this rank's slice of the global permutation (sorted position -> original id)
+      base        global sorted position of this rank's first query
+    Concatenating rows / permutation of ranks 0..W-1 gives exactly what kn_get_knearests /
+    kn_get_permutation return on one GPU.  The rows live in the handle: call free() when done."""
 
-    def __init__(self, query_ids, rows, info):
-        self.query_ids, self.rows, self.info = query_ids, rows, info
+    def __init__(self, handle, rows, permutation, base, info):
+        self.handle, self.rows, self.permutation, self.base, self.info = handle, rows, permutation, base, info
+
+    def free(self):
+        if self.handle is not None:
+            self.handle.free()
+            self.handle = None
+
+
+class _DevView:
+    def __init__(self, ptr, shape, typestr="<i4"):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
 
 
 def solve_distributed(local_xyz, first_id: int, n_total: int, k: int, group=None, halo: int | None = None,
-                      density: float = 3.1, keep_rows: bool = True) -> SlabRows:
-    """One pass of the multi-GPU hot path on this rank's chunk (CUDA tensor [n_local, 3])."""
+                      density: float = 3.1, phases: dict | None = None, host_rows=None) -> SlabRows:
+    """One pass of the multi-GPU hot path on this rank's chunk (CUDA tensor [n_local, 3]).
+    `phases` (optional dict) receives wall-clock milliseconds per phase, with a device sync after each
+    (diagnostic runs only: the syncs are not free).  `host_rows` (optional page-locked uint32 numpy array with
+    room for this rank's rows) makes the solve stream its rows to the host while computing
+    (knc_solve_to_host)."""
     import torch
     import torch.distributed as dist
     import cuda_knearests_b200 as K
@@ -106,45 +125,72 @@ def solve_distributed(local_xyz, first_id: int, n_total: int, k: int, group=None
     D, zsplit = grid_and_split(n_total, world, density)
     halo = halo_planes(k, density) if halo is None else halo
     info = {"grid_dim": D, "zsplit": zsplit, "attempts": 0}
+    t_last = [time.perf_counter()]
+    dev = local_xyz.device
+
+    def mark(name):
+        if phases is not None:
+            torch.cuda.synchronize()
+            now = time.perf_counter()
+            phases[name] = phases.get(name, 0.0) + 1e3 * (now - t_last[0])
+            t_last[0] = now
+
     while True:
         info["attempts"] += 1
         info["halo"] = halo
         send_xyz, send_ids, counts = route_device(local_xyz, first_id, D, zsplit, halo)
+        mark("route")
         recv_xyz, recv_ids, recv_counts = exchange(send_xyz, send_ids, counts, group)
+        mark("exchange")
         del send_xyz, send_ids
         zb, ze, ozb, oze = held_planes(zsplit, rank, halo, D)
-        ok = 1
-        rows = qids = None
         info.update(points_held=int(recv_xyz.shape[0]), sent=int(sum(counts)), planes=(zb, ze, ozb, oze))
+        p = None
+        mine = [0, 0]
         if oze > ozb and recv_xyz.shape[0] > 0:
             p = K.KnProblem(recv_xyz, k=k, grid_dim=D, slab=(zb, ze, ozb, oze), density=density)
+            mine = [p.info.query_count, p.info.query_begin]
+        mark("prepare")
+        # global sorted position of a local one = local + (queries of all lower ranks - own query_begin)
+        allq = torch.empty((world, 2), dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(allq, torch.tensor(mine, dtype=torch.int64, device=dev), group=group)
+        allq = allq.tolist()
+        base = sum(int(allq[d][0]) for d in range(rank))
+        ok = 1
+        perm = rows = None
+        if p is not None:
+            K._check(K.lib().knc_set_index_offset(p._h, base - p.info.query_begin))
             try:
-                p.solve()
+                if host_rows is not None:
+                    p.solve_to_host(host_rows, chunks=8)
+                else:
+                    p.solve()
+                mark("solve")
                 info.update(p.timings(), queries=p.info.query_count)
-                if keep_rows:
-                    nq = p.info.query_count
-                    rows = torch.empty((nq, k), dtype=torch.int32, device=recv_xyz.device)
-                    qids = torch.empty((nq,), dtype=torch.int32, device=recv_xyz.device)
-                    torch.cuda.current_stream().synchronize()
-                    K._check(K.lib().knc_get_knearests_global(p._h, C.c_void_p(recv_ids.data_ptr()),
-                                                              C.c_void_p(rows.data_ptr()), C.c_void_p(qids.data_ptr())))
+                perm = torch.empty((p.info.query_count,), dtype=torch.int32, device=dev)
+                torch.cuda.current_stream().synchronize()
+                K._check(K.lib().knc_get_permutation_global(p._h, C.c_void_p(recv_ids.data_ptr()), C.c_void_p(perm.data_ptr())))
+                rows = torch.as_tensor(_DevView(p.info.d_knearests, (p.info.query_count, k)), device=dev)
             except K.KnError as e:
                 if e.code != 5:  # KNC_ERR_HALO
                     raise
                 ok = 0
-            finally:
-                p.free()
-        flag = torch.tensor([ok], dtype=torch.int32, device=local_xyz.device)
+        mark("permutation_slice")
+        flag = torch.tensor([ok], dtype=torch.int32, device=dev)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        mark("halo_vote")
         if int(flag.item()) == 1:
-            return SlabRows(qids, rows, info)
+            return SlabRows(p, rows, perm, base, info)
+        if p is not None:
+            p.free()
         halo += 2  # some query reached beyond its halo: widen everywhere and repeat (never silently wrong)
 
 
 # ------------------------------------------------------------------------------------------- bench
 def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_config, ClockSampler, measured_peak_gbs):
     """bench.py for N > 1: 100 M points cut into z-slabs, strong scaling.  A step is the whole multi-GPU
-    hot path: route + NCCL all-to-all + kn_prepare (slab) + kn_solve + rows to global ids."""
+    hot path: route + NCCL all-to-all + kn_prepare (slab) + kn_solve (rows in global sorted positions) +
+    this rank's slice of the global permutation."""
     import json
     import torch
     import torch.distributed as dist
@@ -156,24 +202,28 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
     pts = K.generate_uniform_device(hi - lo, seed=SEED, first=lo, device=dev)
 
     def step():
-        return solve_distributed(pts, lo, n, k, density=args.density or 3.1)
+        r = solve_distributed(pts, lo, n, k, density=args.density or 3.1)
+        info = r.info
+        r.free()
+        return info
 
     for _ in range(args.warmup):
-        res = step()
+        step()
     dist.barrier()
     torch.cuda.synchronize()
     infos = []
     with ClockSampler(local_rank) as clk:
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            res = step()
-            infos.append(res.info)
+            infos.append(step())
         torch.cuda.synchronize()
         dist.barrier()
         wall = time.perf_counter() - t0
     t = torch.tensor([wall], dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     wall = float(t.item())
+    phase_ms = {}
+    solve_distributed(pts, lo, n, k, density=args.density or 3.1, phases=phase_ms).free()  # untimed, instrumented
     stats = torch.tensor([infos[-1].get("solve_ms", 0.0), infos[-1].get("build_ms", 0.0),
                           float(infos[-1].get("queries", 0)), float(infos[-1]["points_held"]),
                           float(infos[-1]["sent"])], dtype=torch.float64, device=dev)
@@ -187,14 +237,15 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
         nq_max = int(max(s[2].item() for s in allstats))
         host_rows = torch.empty((nq_max + 1024, k), dtype=torch.int32, pin_memory=True)
         host_qid = torch.empty((nq_max + 1024,), dtype=torch.int32, pin_memory=True)
+        host_rows_np = host_rows.numpy().view(np.uint32)
 
         def step_e2e():
             d_in = host_in.to(dev, non_blocking=True)
-            r = solve_distributed(d_in, lo, n, k, density=args.density or 3.1)
+            r = solve_distributed(d_in, lo, n, k, density=args.density or 3.1, host_rows=host_rows_np)
             nq = r.rows.shape[0]
-            host_rows[:nq].copy_(r.rows, non_blocking=True)
-            host_qid[:nq].copy_(r.query_ids, non_blocking=True)
+            host_qid[:nq].copy_(r.permutation, non_blocking=True)
             torch.cuda.synchronize()
+            r.free()
 
         step_e2e()
         dist.barrier()
@@ -208,8 +259,9 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
         e2e = {"value": n / float(te.item()), "unit": UNIT, "h2d_bytes_per_step": 12 * n,
                "d2h_bytes_per_step": 4 * k * n + 4 * n, "ms_per_step": 1e3 * float(te.item()), "steps": e_steps,
-               "call": "per rank: pinned host chunk -> device, route + all-to-all + knc_prepare_ex(slab) + knc_solve + "
-                       "knc_get_knearests_global, rows and query ids -> pinned host"}
+               "call": "per rank: pinned host chunk -> device, route + all-to-all + knc_prepare_ex(slab) + knc_solve_to_host + "
+                       "knc_get_permutation_global; rows (global sorted positions) stream to pinned host memory during the solve "
+                       "(knc_solve_to_host), permutation slice copied after"}
 
     if rank == 0:
         peak, peak_kind = measured_peak_gbs()
@@ -225,7 +277,7 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
         line = {"metric": METRIC, "value": n / (wall / args.steps), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
-                "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 12 * args.steps * world,
+                "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 12 * args.steps * world,  # per rank: route 3, build 6, query 2, permutation slice 1
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": None, "kernel": "kn_query_select_kernel (slowest rank)",
                              "kernel_ms": float(allstats[worst][0].item()),
@@ -234,7 +286,8 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
                 "cpu_baseline": None,
                 "device_ms": {"query_max_over_ranks": solve_ms,
                               "grid_build_max_over_ranks": max(float(s[1].item()) for s in allstats)},
-                "queries_per_rank": queries, "halo_attempts": infos[-1]["attempts"]}
+                "queries_per_rank": queries, "halo_attempts": infos[-1]["attempts"],
+                "phase_ms_rank0_instrumented": {kk: round(v, 3) for kk, v in phase_ms.items()}}
         print(json.dumps(line), flush=True)
     dist.barrier()
     dist.destroy_process_group()

@@ -165,6 +165,16 @@ int knc_generate_uniform_device(float *d_xyz, long long first, long long count, 
 int knc_slab_route(const float *d_xyz, int n, unsigned int first_id, int grid_dim, int nranks, const int *zsplit,
                    int halo, float *d_out_xyz, unsigned int *d_out_id, long long capacity, long long *out_counts);
 
+/* Slab handles keep the single-GPU contract globally.  Because every rank holds its planes in global
+ * order, local sorted position + a constant = GLOBAL sorted position (the constant: points in all lower
+ * planes minus this handle's query_begin; the caller gets it from an all-gather of the ranks' query
+ * counts).  knc_set_index_offset makes the next knc_solve store rows in global sorted positions
+ * directly (no extra pass); knc_get_permutation_global writes this rank's slice of the global
+ * permutation, d_out[i] = d_ids[perm[query_begin + i]] (DEVICE, query_count entries).  Concatenated over
+ * the ranks, rows and permutation are exactly what one GPU would return (knearests.cu:57,144-147). */
+int knc_set_index_offset(knc_problem *p, long long offset);
+int knc_get_permutation_global(knc_problem *p, const unsigned int *d_ids, unsigned int *d_out);
+
 /* Rows of a solved (slab) handle in GLOBAL ids: d_ids[i] (DEVICE) is the global id of the handle's i-th
  * input point; d_out_rows (DEVICE, query_count*k) gets ids[perm[knn]], d_out_query_ids (DEVICE,
  * query_count, may be NULL) the global id of each row's query.  (The reference's index remap,

@@ -30,13 +30,15 @@ def test_route_kernel_is_the_stable_multisplit(kn, oracle):
 
 @pytest.mark.parametrize("world,k,n", [(2, 20, 400_000), (4, 8, 600_000), (8, 20, 1_000_000), (3, 50, 300_000)])
 def test_emulated_ranks_reproduce_single_gpu_rows(kn, oracle, world, k, n):
+    """Rows in GLOBAL sorted positions + permutation slices of the ranks, concatenated, are exactly the
+    single-GPU kn_get_knearests / kn_get_permutation arrays; and the same rows in original ids
+    (knc_get_knearests_global) are the single-GPU rows in original ids."""
     import torch
     from cuda_knearests_b200 import slabs
     pts = oracle.generate_uniform(n, seed=20171004)
-    # single GPU, rows in original ids
     with kn.KnProblem(pts, k=k) as p:
         p.solve()
-        want = p.get_knearests_original()
+        want_rows, want_perm, want_orig = p.get_knearests(), p.get_permutation(), p.get_knearests_original()
     D, zsplit = slabs.grid_and_split(n, world)
     halo = slabs.halo_planes(k)
     dev = torch.from_numpy(pts).cuda()
@@ -45,23 +47,32 @@ def test_emulated_ranks_reproduce_single_gpu_rows(kn, oracle, world, k, n):
         lo, hi = r * n // world, (r + 1) * n // world
         sx, si, counts = slabs.route_device(dev[lo:hi].contiguous(), lo, D, zsplit, halo)
         routed.append((sx, si, np.concatenate([[0], np.cumsum(counts)])))
-    got = np.full((n, k), 0xFFFFFFFF, np.uint32)
-    seen = np.zeros(n, bool)
+    got_rows, got_perm = [], []
+    got_orig = np.full((n, k), 0xFFFFFFFF, np.uint32)
+    base = 0
     for d in range(world):
         rx = torch.cat([sx[off[d]:off[d + 1]] for sx, _, off in routed]).contiguous()
         ri = torch.cat([si[off[d]:off[d + 1]] for _, si, off in routed]).contiguous()
         zb, ze, ozb, oze = slabs.held_planes(zsplit, d, halo, D)
         with kn.KnProblem(rx, k=k, grid_dim=D, slab=(zb, ze, ozb, oze)) as p:
-            p.solve()
             nq = p.info.query_count
+            # original ids first (no offset), then the global-position form
+            p.solve()
             rows = torch.empty((nq, k), dtype=torch.int32, device="cuda")
             qid = torch.empty((nq,), dtype=torch.int32, device="cuda")
             torch.cuda.synchronize()
             kn._check(kn.lib().knc_get_knearests_global(p._h, C.c_void_p(ri.data_ptr()), C.c_void_p(rows.data_ptr()),
                                                         C.c_void_p(qid.data_ptr())))
-        q = qid.cpu().numpy()
-        assert not seen[q].any()
-        seen[q] = True
-        got[q] = rows.cpu().numpy().view(np.uint32)
-    assert seen.all()                      # every point is a query of exactly one rank
-    assert np.array_equal(got, want)       # and its row is the single-GPU row
+            got_orig[qid.cpu().numpy()] = rows.cpu().numpy().view(np.uint32)
+            kn._check(kn.lib().knc_set_index_offset(p._h, base - p.info.query_begin))
+            p.solve()
+            got_rows.append(p.get_knearests())
+            perm = torch.empty((nq,), dtype=torch.int32, device="cuda")
+            torch.cuda.synchronize()
+            kn._check(kn.lib().knc_get_permutation_global(p._h, C.c_void_p(ri.data_ptr()), C.c_void_p(perm.data_ptr())))
+            got_perm.append(perm.cpu().numpy().view(np.uint32))
+            base += nq
+    assert base == n                                            # every point is a query of exactly one rank
+    assert np.array_equal(np.concatenate(got_perm), want_perm)  # global permutation, slice by slice
+    assert np.array_equal(np.concatenate(got_rows), want_rows)  # rows in global sorted positions
+    assert np.array_equal(got_orig, want_orig)                  # rows in original ids
