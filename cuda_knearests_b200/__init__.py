@@ -48,7 +48,7 @@ class Options(C.Structure):  # knc_options
     _fields_ = [("struct_size", C.c_size_t), ("k", C.c_int), ("density", C.c_float),
                 ("points_on_device", C.c_int), ("grid_dim", C.c_int), ("z_begin", C.c_int),
                 ("z_end", C.c_int), ("own_z_begin", C.c_int), ("own_z_end", C.c_int),
-                ("search_scale", C.c_float), ("algorithm", C.c_int)]
+                ("search_scale", C.c_float), ("algorithm", C.c_int), ("point_stride", C.c_int)]
 
 
 class Info(C.Structure):  # knc_info
@@ -101,11 +101,11 @@ def lib() -> C.CDLL:
         L.knc_grid_dim.argtypes = [C.c_int, C.c_float]
         L.knc_generate_uniform_device.argtypes = [vp, C.c_longlong, C.c_longlong, C.c_uint64]
         L.knc_scan_cells_noalloc.argtypes = [vp, C.c_longlong, vp, vp]
-        L.knc_slab_route.argtypes = [vp, C.c_int, C.c_uint, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, vp, vp,
+        L.knc_slab_route.argtypes = [vp, C.c_int, C.c_uint, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, vp,
                                      C.c_longlong, C.POINTER(C.c_longlong)]
-        L.knc_get_knearests_global.argtypes = [vp, vp, vp, vp]
+        L.knc_get_knearests_global.argtypes = [vp, vp, C.c_int, vp, vp]
         L.knc_set_index_offset.argtypes = [vp, C.c_longlong]
-        L.knc_get_permutation_global.argtypes = [vp, vp, vp]
+        L.knc_get_permutation_global.argtypes = [vp, vp, C.c_int, vp]
         L.knc_last_error.restype = C.c_char_p
         L.knc_version.restype = C.c_char_p
         _lib = L
@@ -129,7 +129,8 @@ class KnProblem:
     """One point cloud on one GPU -- the reference's ``kn_problem`` handle (knearests.h:3-16).
 
     ``points`` is either a host array (anything numpy can view as float32 [n,3]; copied to the device,
-    as kn_prepare does, knearests.cu:308-311) or a CUDA ``torch.Tensor`` float32 [n,3] (used in place).
+    as kn_prepare does, knearests.cu:308-311) or a CUDA ``torch.Tensor`` float32 [n,3] (used in place);
+    a CUDA tensor [n,4] is read as 16-byte records x, y, z, ignored word (knc_options.point_stride = 4).
     """
 
     def __init__(self, points, k: int = 0, density: float = 0.0, grid_dim: int = 0, slab=None,
@@ -147,9 +148,11 @@ class KnProblem:
         if hasattr(points, "is_cuda"):
             import torch
             if not points.is_cuda or points.dtype != torch.float32 or not points.is_contiguous():
-                raise ValueError("device input must be a contiguous CUDA float32 tensor [n,3]")
+                raise ValueError("device input must be a contiguous CUDA float32 tensor [n,3] or [n,4]")
             torch.cuda.current_stream(points.device).synchronize()  # the library works on its own stream
-            n = points.numel() // 3
+            stride = 4 if (points.dim() == 2 and points.shape[1] == 4) else 3
+            opt.point_stride = stride
+            n = points.numel() // stride
             opt.points_on_device = 1
             self._keep = points
             ptr = C.c_void_p(points.data_ptr())

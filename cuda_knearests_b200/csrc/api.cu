@@ -14,6 +14,9 @@
 
 #include <limits.h>
 
+#include <mutex>
+#include <vector>
+
 #include "kn_internal.h"
 #include "params.h"
 
@@ -67,6 +70,33 @@ void keep_pool_memory(int device) {
     done[device] = true;
 }
 
+// Streams and events are recycled: creating and destroying them are kernel-mode driver calls that cost
+// a noticeable fraction of a millisecond each, more when several processes share the host (one per GPU).
+struct StreamKit { cudaStream_t stream; cudaEvent_t ev[4]; };
+std::mutex g_kit_lock;
+std::vector<StreamKit> g_kits[64];
+
+cudaError_t take_kit(int device, StreamKit *k) {
+    {
+        std::lock_guard<std::mutex> hold(g_kit_lock);
+        if (device >= 0 && device < 64 && !g_kits[device].empty()) {
+            *k = g_kits[device].back();
+            g_kits[device].pop_back();
+            return cudaSuccess;
+        }
+    }
+    cudaError_t e = cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking);
+    for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreate(&k->ev[i]);
+    return e;
+}
+
+void give_kit(int device, const StreamKit &k) {
+    std::lock_guard<std::mutex> hold(g_kit_lock);
+    if (device >= 0 && device < 64 && g_kits[device].size() < 16) { g_kits[device].push_back(k); return; }
+    cudaStreamDestroy(k.stream);
+    for (int i = 0; i < 4; ++i) cudaEventDestroy(k.ev[i]);
+}
+
 int default_k() {
     const char *e = getenv("KN_NB_PLANES");
     if (e && atoi(e) > 0) return atoi(e);
@@ -81,11 +111,12 @@ void free_device_state(knc_problem *p) {
         if (q) cudaFreeAsync(q, st);
     if (st) {
         cudaStreamSynchronize(st);
-        cudaStreamDestroy(st);
+        StreamKit k;
+        k.stream = st;
+        for (int i = 0; i < 4; ++i) k.ev[i] = p->ev[i];
+        give_kit(p->device, k);
     }
     if (p->copy_stream) cudaStreamDestroy(p->copy_stream);
-    for (cudaEvent_t &e : p->ev)
-        if (e) cudaEventDestroy(e);
 }
 
 }  // namespace
@@ -128,6 +159,8 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     const int k = o.k > 0 ? o.k : default_k();
     if (k > KNC_MAX_K) return fail(KNC_ERR_INVALID, "knc_prepare: k = %d exceeds KNC_MAX_K = %d", k, KNC_MAX_K);
     const float density = o.density > 0.f ? o.density : 3.1f;
+    const int stride = o.point_stride > 0 ? o.point_stride : 3;
+    if (stride != 3 && stride != 4) return fail(KNC_ERR_INVALID, "knc_prepare: point_stride = %d, supported 3 or 4", stride);
     const int D = o.grid_dim > 0 ? o.grid_dim : knc_grid_dim(n, density);
     if ((long long)D * D * D > 2000000000ll) return fail(KNC_ERR_INVALID, "knc_prepare: grid %d^3 too large", D);
     int zb = 0, ze = D, ozb = 0, oze = D;
@@ -149,9 +182,13 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
 
     CU(cudaGetDevice(&p->device));
     keep_pool_memory(p->device);
-    CU(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+    {
+        StreamKit kit;
+        CU(take_kit(p->device, &kit));
+        p->stream = kit.stream;
+        for (int i = 0; i < 4; ++i) p->ev[i] = kit.ev[i];
+    }
     st = p->stream;
-    for (cudaEvent_t &e : p->ev) CU(cudaEventCreate(&e));
     p->k = k; p->density = density; p->search_scale = o.search_scale > 0.f ? o.search_scale : 1.f;
     p->algorithm = o.algorithm;
     p->z_begin = zb; p->z_end = ze; p->own_z_begin = ozb; p->own_z_end = oze;
@@ -181,12 +218,12 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     if (o.points_on_device) {
         d_in = const_cast<float *>(xyz);
     } else {  // knearests.cu:308-311
-        CU(dev_alloc((void **)&d_in, sizeof(float) * 3 * (size_t)n, st));
-        CU(cudaMemcpyAsync(d_in, xyz, sizeof(float) * 3 * (size_t)n, cudaMemcpyHostToDevice, st));
+        CU(dev_alloc((void **)&d_in, sizeof(float) * stride * (size_t)n, st));
+        CU(cudaMemcpyAsync(d_in, xyz, sizeof(float) * stride * (size_t)n, cudaMemcpyHostToDevice, st));
     }
     g.D = D; g.zb = zb; g.ze = ze; g.Df = (float)D; g.w = 1000.f / (float)D; g.invw = (float)D / 1000.f;
     CU(cudaEventRecord(p->ev[1], st));
-    CU(kn_launch_build(d_in, n, g, cells, p->pub.d_counters, p->pub.d_ptrs, p->pub.d_globcounter,
+    CU(kn_launch_build(d_in, stride, n, g, cells, p->pub.d_counters, p->pub.d_ptrs, p->pub.d_globcounter,
                        p->pub.d_permutation, (float *)p->pub.d_stored_points, p->d_points4, s, st));
     CU(cudaEventRecord(p->ev[2], st));
     CU(cudaMemsetAsync(p->pub.d_cell_max, 0, sizeof(float), st));

@@ -39,18 +39,28 @@ __device__ __forceinline__ int axis_cell(float p, float Df, int lo, int hi) {
 // One point per thread; a block stages its 256 points (768 floats) through shared memory with
 // float4 loads, so global reads are 16-byte vectorised and fully coalesced although the input is AoS.
 __global__ void __launch_bounds__(kBuildThreads)
-kn_count_kernel(const float *__restrict__ xyz, int n, GridGeom g, int *__restrict__ counters,
+kn_count_kernel(const float *__restrict__ xyz, int stride, int n, GridGeom g, int *__restrict__ counters,
                 int *__restrict__ cellid, int *__restrict__ rank, int aligned16) {
     __shared__ __align__(16) float tile[kBuildThreads * 3];
     const int tid = threadIdx.x;
     const long long first = (long long)blockIdx.x * kBuildThreads;
     const int here = (int)min((long long)kBuildThreads, (long long)n - first);
-    const float *src = xyz + first * 3;
-    if (aligned16 && here == kBuildThreads) {
-        if (tid < kBuildThreads * 3 / 4)
-            reinterpret_cast<float4 *>(tile)[tid] = __ldg(reinterpret_cast<const float4 *>(src) + tid);
+    if (stride == 4) {  // 16-byte records (x, y, z, payload): one aligned float4 load per point, payload ignored
+        if (tid < here) {
+            const float *rec = xyz + (first + tid) * 4;
+            float4 v;
+            if (aligned16) v = __ldg(reinterpret_cast<const float4 *>(rec));
+            else v = make_float4(__ldg(rec), __ldg(rec + 1), __ldg(rec + 2), 0.f);
+            tile[3 * tid] = v.x; tile[3 * tid + 1] = v.y; tile[3 * tid + 2] = v.z;
+        }
     } else {
-        for (int i = tid; i < here * 3; i += kBuildThreads) tile[i] = __ldg(src + i);
+        const float *src = xyz + first * 3;
+        if (aligned16 && here == kBuildThreads) {
+            if (tid < kBuildThreads * 3 / 4)
+                reinterpret_cast<float4 *>(tile)[tid] = __ldg(reinterpret_cast<const float4 *>(src) + tid);
+        } else {
+            for (int i = tid; i < here * 3; i += kBuildThreads) tile[i] = __ldg(src + i);
+        }
     }
     __syncthreads();
     const bool valid = tid < here;
@@ -260,7 +270,7 @@ kn_order_big_kernel(const int *big_count, const int *__restrict__ big_list, cons
 
 // --------------------------------------------------------------------------------------- gather
 __global__ void __launch_bounds__(kBuildThreads)
-kn_gather_kernel(const float *__restrict__ xyz, int n, const unsigned int *__restrict__ permutation,
+kn_gather_kernel(const float *__restrict__ xyz, int stride, int n, const unsigned int *__restrict__ permutation,
                  float *__restrict__ points3, float4 *__restrict__ points4) {
     __shared__ float tile[kBuildThreads * 3];
     const int tid = threadIdx.x;
@@ -269,7 +279,8 @@ kn_gather_kernel(const float *__restrict__ xyz, int n, const unsigned int *__res
     const int here = (int)min((long long)kBuildThreads, (long long)n - first);
     if (s < n) {
         const unsigned i = __ldg(permutation + s);
-        const float x = __ldg(xyz + 3ll * i), y = __ldg(xyz + 3ll * i + 1), z = __ldg(xyz + 3ll * i + 2);
+        const float *rec = xyz + (long long)stride * i;
+        const float x = __ldg(rec), y = __ldg(rec + 1), z = __ldg(rec + 2);
         points4[s] = make_float4(x, y, z, __uint_as_float(i));
         tile[3 * tid] = x; tile[3 * tid + 1] = y; tile[3 * tid + 2] = z;
     }
@@ -313,7 +324,7 @@ inline unsigned blocks_for(long long items, int per_block) {
 
 size_t kn_build_scratch_tiles(long long cells) { return (size_t)((cells + kScanTile - 1) / kScanTile); }
 
-cudaError_t kn_launch_build(const float *d_in_xyz, int n, const GridGeom &g, long long cells, int *d_counters,
+cudaError_t kn_launch_build(const float *d_in_xyz, int stride, int n, const GridGeom &g, long long cells, int *d_counters,
                             int *d_ptrs, int *d_globcounter, unsigned int *d_permutation, float *d_points3,
                             float4 *d_points4, const BuildScratch &s, cudaStream_t st) {
     cudaError_t e;
@@ -321,7 +332,7 @@ cudaError_t kn_launch_build(const float *d_in_xyz, int n, const GridGeom &g, lon
     if ((e = cudaMemsetAsync(s.d_tile, 0, sizeof(unsigned long long) * s.tile_count, st)) != cudaSuccess) return e;
     if ((e = cudaMemsetAsync(s.d_ticket, 0, sizeof(int) * 2, st)) != cudaSuccess) return e;
     const int aligned16 = ((uintptr_t)d_in_xyz & 15u) == 0;
-    kn_count_kernel<<<blocks_for(n, kBuildThreads), kBuildThreads, 0, st>>>(d_in_xyz, n, g, d_counters,
+    kn_count_kernel<<<blocks_for(n, kBuildThreads), kBuildThreads, 0, st>>>(d_in_xyz, stride, n, g, d_counters,
                                                                            s.d_cellid, s.d_rank, aligned16);
     kn_scan_kernel<<<(unsigned)s.tile_count, kBuildThreads, 0, st>>>(d_counters, d_ptrs, cells, s.d_tile,
                                                                     s.d_ticket, d_globcounter);
@@ -330,7 +341,7 @@ cudaError_t kn_launch_build(const float *d_in_xyz, int n, const GridGeom &g, lon
     kn_order_kernel<<<blocks_for(cells, kBuildThreads), kBuildThreads, 0, st>>>(cells, d_ptrs, d_permutation,
                                                                                s.d_ticket + 1, s.d_biglist);
     kn_order_big_kernel<<<148, 1024, 0, st>>>(s.d_ticket + 1, s.d_biglist, d_ptrs, d_permutation);
-    kn_gather_kernel<<<blocks_for(n, kBuildThreads), kBuildThreads, 0, st>>>(d_in_xyz, n, d_permutation,
+    kn_gather_kernel<<<blocks_for(n, kBuildThreads), kBuildThreads, 0, st>>>(d_in_xyz, stride, n, d_permutation,
                                                                             d_points3, d_points4);
     return cudaGetLastError();
 }

@@ -49,7 +49,7 @@ struct BuildScratch {
     size_t tile_count;
 };
 size_t kn_build_scratch_tiles(long long cells);
-cudaError_t kn_launch_build(const float *d_in_xyz, int n, const GridGeom &g, long long cells, int *d_counters,
+cudaError_t kn_launch_build(const float *d_in_xyz, int stride, int n, const GridGeom &g, long long cells, int *d_counters,
                             int *d_ptrs, int *d_globcounter, unsigned int *d_permutation, float *d_points3,
                             float4 *d_points4, const BuildScratch &s, cudaStream_t st);
 cudaError_t kn_launch_generate(float *d_xyz, long long first, long long count, uint64_t seed, cudaStream_t st);

@@ -90,8 +90,7 @@ __global__ void __launch_bounds__(1024) kn_route_scan_kernel(int *counts, int nb
 __global__ void __launch_bounds__(kRouteThreads)
 kn_route_scatter_kernel(const float *__restrict__ xyz, int n, unsigned first_id, float Df, int D,
                         const __grid_constant__ RoutePlan pl, int nblocks, const int *__restrict__ offsets,
-                        const long long *__restrict__ base, float *__restrict__ out_xyz,
-                        unsigned *__restrict__ out_id) {
+                        const long long *__restrict__ base, float4 *__restrict__ out_rec) {
     __shared__ int s_warp[kMaxRanks][kRouteThreads / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const long long i = (long long)blockIdx.x * kRouteThreads + tid;
@@ -112,38 +111,41 @@ kn_route_scatter_kernel(const float *__restrict__ xyz, int n, unsigned first_id,
             int before = __popc(b & ((1u << lane) - 1u));
             for (int wq = 0; wq < warp; ++wq) before += s_warp[d][wq];
             const long long pos = base[d] + offsets[(size_t)d * nblocks + blockIdx.x] + before;
-            out_xyz[3 * pos] = x; out_xyz[3 * pos + 1] = y; out_xyz[3 * pos + 2] = z;
-            out_id[pos] = first_id + (unsigned)i;
+            out_rec[pos] = make_float4(x, y, z, __uint_as_float(first_id + (unsigned)i));  // one 16-byte store
         }
     }
 }
 
 // rows[r*k + j] = ids[perm[knn[r*k + j]]], query_ids[r] = ids[perm[query_begin + r]]
 __global__ void kn_rows_to_global_kernel(const unsigned *__restrict__ knn, const unsigned *__restrict__ perm,
-                                         const unsigned *__restrict__ ids, int query_begin, long long total, int k,
-                                         unsigned *__restrict__ out_rows, unsigned *__restrict__ out_query_ids) {
+                                         const unsigned *__restrict__ ids, int id_stride, int query_begin,
+                                         long long total, int k, unsigned *__restrict__ out_rows,
+                                         unsigned *__restrict__ out_query_ids) {
     const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= total) return;
     const unsigned v = __ldg(knn + e);
-    out_rows[e] = v == KNC_EMPTY ? KNC_EMPTY : __ldg(ids + __ldg(perm + v));
+    out_rows[e] = v == KNC_EMPTY ? KNC_EMPTY : __ldg(ids + (size_t)id_stride * __ldg(perm + v));
     const long long r = e / k;
-    if (out_query_ids && e - r * k == 0) out_query_ids[r] = __ldg(ids + __ldg(perm + query_begin + r));
+    if (out_query_ids && e - r * k == 0)
+        out_query_ids[r] = __ldg(ids + (size_t)id_stride * __ldg(perm + query_begin + r));
 }
 
 // out[i] = ids[perm[query_begin + i]]: this rank's slice of the global permutation
 __global__ void kn_perm_to_global_kernel(const unsigned *__restrict__ perm, const unsigned *__restrict__ ids,
-                                         int query_begin, int count, unsigned *__restrict__ out) {
+                                         int id_stride, int query_begin, int count, unsigned *__restrict__ out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < count) out[i] = __ldg(ids + __ldg(perm + query_begin + i));
+    if (i < count) out[i] = __ldg(ids + (size_t)id_stride * __ldg(perm + query_begin + i));
 }
 
 }  // namespace
 
-extern "C" int knc_get_permutation_global(knc_problem *p, const unsigned int *d_ids, unsigned int *d_out) {
-    if (!p || !d_ids || !d_out) return kn_set_error(KNC_ERR_INVALID, "knc_get_permutation_global: NULL argument");
+extern "C" int knc_get_permutation_global(knc_problem *p, const unsigned int *d_ids, int id_stride,
+                                          unsigned int *d_out) {
+    if (!p || !d_ids || !d_out || id_stride < 1)
+        return kn_set_error(KNC_ERR_INVALID, "knc_get_permutation_global: bad argument");
     if (p->query_count > 0) {
         kn_perm_to_global_kernel<<<(unsigned)((p->query_count + 255) / 256), 256, 0, p->stream>>>(
-            p->pub.d_permutation, d_ids, p->query_begin, p->query_count, d_out);
+            p->pub.d_permutation, d_ids, id_stride, p->query_begin, p->query_count, d_out);
         cudaError_t e = cudaGetLastError();
         if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
         if (e != cudaSuccess) return kn_set_error(KNC_ERR_CUDA, "knc_get_permutation_global: %s", cudaGetErrorString(e));
@@ -152,9 +154,10 @@ extern "C" int knc_get_permutation_global(knc_problem *p, const unsigned int *d_
 }
 
 extern "C" int knc_slab_route(const float *d_xyz, int n, unsigned int first_id, int grid_dim, int nranks,
-                              const int *zsplit, int halo, float *d_out_xyz, unsigned int *d_out_id,
-                              long long capacity, long long *out_counts) {
-    if (!d_xyz || !zsplit || !d_out_xyz || !d_out_id || !out_counts || n < 0 || grid_dim < 1 || halo < 0)
+                              const int *zsplit, int halo, float *d_out_rec, long long capacity,
+                              long long *out_counts) {
+    if (!d_xyz || !zsplit || !d_out_rec || !out_counts || n < 0 || grid_dim < 1 || halo < 0 ||
+        ((uintptr_t)d_out_rec & 15u))
         return kn_set_error(KNC_ERR_INVALID, "knc_slab_route: bad argument");
     if (nranks < 1 || nranks > kMaxRanks)
         return kn_set_error(KNC_ERR_INVALID, "knc_slab_route: nranks = %d, supported 1..%d", nranks, kMaxRanks);
@@ -192,8 +195,8 @@ extern "C" int knc_slab_route(const float *d_xyz, int n, unsigned int first_id, 
             e = cudaMemcpyAsync(d_tot + kMaxRanks, h + kMaxRanks, sizeof(long long) * nranks, cudaMemcpyHostToDevice, st);
             if (e == cudaSuccess) {
                 kn_route_scatter_kernel<<<nblocks, kRouteThreads, 0, st>>>(d_xyz, n, first_id, (float)grid_dim, grid_dim, pl,
-                                                                          nblocks, d_counts, d_tot + kMaxRanks, d_out_xyz,
-                                                                          d_out_id);
+                                                                          nblocks, d_counts, d_tot + kMaxRanks,
+                                                                          reinterpret_cast<float4 *>(d_out_rec));
                 e = cudaGetLastError();
             }
             if (e == cudaSuccess) e = cudaStreamSynchronize(st);
@@ -205,14 +208,16 @@ extern "C" int knc_slab_route(const float *d_xyz, int n, unsigned int first_id, 
     return rc;
 }
 
-extern "C" int knc_get_knearests_global(knc_problem *p, const unsigned int *d_ids, unsigned int *d_out_rows,
-                                        unsigned int *d_out_query_ids) {
-    if (!p || !d_ids || !d_out_rows) return kn_set_error(KNC_ERR_INVALID, "knc_get_knearests_global: NULL argument");
+extern "C" int knc_get_knearests_global(knc_problem *p, const unsigned int *d_ids, int id_stride,
+                                        unsigned int *d_out_rows, unsigned int *d_out_query_ids) {
+    if (!p || !d_ids || !d_out_rows || id_stride < 1)
+        return kn_set_error(KNC_ERR_INVALID, "knc_get_knearests_global: bad argument");
     if (!p->solved) return kn_set_error(KNC_ERR_STATE, "knc_get_knearests_global: call knc_solve first");
     const long long total = (long long)p->query_count * p->k;
     if (total > 0) {
         kn_rows_to_global_kernel<<<(unsigned)((total + 255) / 256), 256, 0, p->stream>>>(
-            p->pub.d_knearests, p->pub.d_permutation, d_ids, p->query_begin, total, p->k, d_out_rows, d_out_query_ids);
+            p->pub.d_knearests, p->pub.d_permutation, d_ids, id_stride, p->query_begin, total, p->k, d_out_rows,
+            d_out_query_ids);
         cudaError_t e = cudaGetLastError();
         if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
         if (e != cudaSuccess) return kn_set_error(KNC_ERR_CUDA, "knc_get_knearests_global: %s", cudaGetErrorString(e));

@@ -55,7 +55,10 @@ typedef struct {
     int z_begin, z_end;
     int own_z_begin, own_z_end;
     float search_scale;     /* tuning: multiplies the first-guess search radius; default 1             */
-    int algorithm;          /* 0 = automatic (fast kernel + retry), 1 = general kernel only (testing)  */
+    int algorithm;          /* 0 = automatic (select/insertion kernel + retry), 1 = general kernel only,
+                               2 = insertion kernel for every k (testing, A/B)                          */
+    int point_stride;       /* floats per input point: 3 (xyz, default) or 4 (xyz + one ignored word,
+                               e.g. the records knc_slab_route writes)                                  */
 } knc_options;
 
 /* What the handle holds; device pointers are valid until knc_free. */
@@ -158,28 +161,30 @@ int knc_generate_uniform_device(float *d_xyz, long long first, long long count, 
  * the device work before and after.
  *
  * knc_slab_route: stable multi-split of n local points (DEVICE xyz, global ids first_id .. first_id+n-1)
- * into per-destination groups: d_out_xyz / d_out_id (DEVICE, room for `capacity` records) receive, for
- * d = 0..nranks-1 in turn, every point whose plane lies in [zsplit[d]-halo, zsplit[d+1]+halo), in input
- * order; out_counts[d] (HOST) is the size of group d.  zsplit is a HOST array of nranks+1 planes rising
+ * into per-destination groups: d_out_rec (DEVICE, room for `capacity` 16-byte records x, y, z, id -- one
+ * buffer, so that one all-to-all moves everything) receives, for d = 0..nranks-1 in turn, every point whose
+ * plane lies in [zsplit[d]-halo, zsplit[d+1]+halo), in input order; out_counts[d] (HOST) is the size of
+ * group d.  A received buffer goes to knc_prepare_ex with point_stride = 4; its 4th words are the id table
+ * for knc_get_permutation_global / knc_get_knearests_global (id_stride = 4).  zsplit is a HOST array of nranks+1 planes rising
  * from 0 to grid_dim.  KNC_ERR_NOMEM if the groups do not fit `capacity` (out_counts is still filled). */
 int knc_slab_route(const float *d_xyz, int n, unsigned int first_id, int grid_dim, int nranks, const int *zsplit,
-                   int halo, float *d_out_xyz, unsigned int *d_out_id, long long capacity, long long *out_counts);
+                   int halo, float *d_out_rec, long long capacity, long long *out_counts);
 
 /* Slab handles keep the single-GPU contract globally.  Because every rank holds its planes in global
  * order, local sorted position + a constant = GLOBAL sorted position (the constant: points in all lower
  * planes minus this handle's query_begin; the caller gets it from an all-gather of the ranks' query
  * counts).  knc_set_index_offset makes the next knc_solve store rows in global sorted positions
  * directly (no extra pass); knc_get_permutation_global writes this rank's slice of the global
- * permutation, d_out[i] = d_ids[perm[query_begin + i]] (DEVICE, query_count entries).  Concatenated over
+ * permutation, d_out[i] = d_ids[id_stride * perm[query_begin + i]] (DEVICE, query_count entries).  Concatenated over
  * the ranks, rows and permutation are exactly what one GPU would return (knearests.cu:57,144-147). */
 int knc_set_index_offset(knc_problem *p, long long offset);
-int knc_get_permutation_global(knc_problem *p, const unsigned int *d_ids, unsigned int *d_out);
+int knc_get_permutation_global(knc_problem *p, const unsigned int *d_ids, int id_stride, unsigned int *d_out);
 
-/* Rows of a solved (slab) handle in GLOBAL ids: d_ids[i] (DEVICE) is the global id of the handle's i-th
- * input point; d_out_rows (DEVICE, query_count*k) gets ids[perm[knn]], d_out_query_ids (DEVICE,
+/* Rows of a solved (slab) handle in GLOBAL ids: d_ids[id_stride * i] (DEVICE) is the global id of the handle's
+ * i-th input point; d_out_rows (DEVICE, query_count*k) gets ids[perm[knn]], d_out_query_ids (DEVICE,
  * query_count, may be NULL) the global id of each row's query.  (The reference's index remap,
  * test_knearests.cu:155-160, extended by the global id table.) */
-int knc_get_knearests_global(knc_problem *p, const unsigned int *d_ids, unsigned int *d_out_rows,
+int knc_get_knearests_global(knc_problem *p, const unsigned int *d_ids, int id_stride, unsigned int *d_out_rows,
                              unsigned int *d_out_query_ids);
 
 /* ---- for callers that must not allocate --------------------------------------------------------

@@ -22,7 +22,12 @@ def numpy_route(xyz, first_id, D, zsplit, halo):
         want = (plane >= zsplit[d] - halo) & (plane < zsplit[d + 1] + halo)
         groups.append((xyz[want], ids[want]))
         counts.append(int(want.sum()))
-    return (np.concatenate([g[0] for g in groups]), np.concatenate([g[1] for g in groups]), counts)
+    xyz_all = np.concatenate([g[0] for g in groups])
+    ids_all = np.concatenate([g[1] for g in groups])
+    rec = np.empty((len(ids_all), 4), np.float32)  # the 16-byte records: x, y, z, bits(id)
+    rec[:, :3] = xyz_all
+    rec[:, 3] = ids_all.view(np.float32)
+    return rec, counts
 
 
 def _worker(rank, world, port, n, k, out_dir):
@@ -37,9 +42,10 @@ def _worker(rank, world, port, n, k, out_dir):
     D, zsplit = slabs.grid_and_split(n, world)
     halo = slabs.halo_planes(k)
     lo, hi = rank * n // world, (rank + 1) * n // world
-    sx, si, counts = numpy_route(pts[lo:hi], lo, D, zsplit, halo)
-    rx, ri, rc = slabs.exchange(torch.from_numpy(sx), torch.from_numpy(si), counts)
-    rx, ri = rx.numpy(), ri.numpy()
+    rec, counts = numpy_route(pts[lo:hi], lo, D, zsplit, halo)
+    rrec, rc = slabs.exchange(torch.from_numpy(rec), counts)
+    rrec = rrec.numpy()
+    rx, ri = np.ascontiguousarray(rrec[:, :3]), np.ascontiguousarray(rrec[:, 3]).view(np.int32)
     zb, ze, ozb, oze = slabs.held_planes(zsplit, rank, halo, D)
     plane = np.clip(np.floor(pts[:, 2] * np.float32(D) / np.float32(1000)).astype(np.int64), 0, D - 1)
     want = np.nonzero((plane >= zb) & (plane < ze))[0]
