@@ -71,17 +71,28 @@ kn_count_kernel(const float *__restrict__ xyz, int stride, int n, GridGeom g, in
         int k = axis_cell(tile[3 * tid + 2], g.Df, g.zb, g.ze - 1) - g.zb;
         cell = i + (j + k * g.D) * g.D;  // z-major, knearests.cu:29
     }
-    // warp-aggregated atomic: lanes in the same cell elect a leader that adds the group size once
-    const unsigned peers = __match_any_sync(0xffffffffu, cell);
+    // Warp-aggregated atomic: lanes in the same cell elect a leader that adds the group size once.
+    // match.any costs one round per distinct value, so it is only used when the warp looks coherent
+    // (some lane shares its cell with its neighbour: sorted or clustered input); a warp of a randomly
+    // ordered cloud -- 32 different cells -- goes straight to 32 plain atomics.
     const int lane = tid & 31;
-    const int leader = __ffs(peers) - 1;
-    const int within = __popc(peers & ((1u << lane) - 1u));
-    int base = 0;
-    if (valid && lane == leader) base = atomicAdd(counters + cell, __popc(peers));
-    base = __shfl_sync(0xffffffffu, base, leader);
+    const int next = __shfl_down_sync(0xffffffffu, cell, 1);
+    const bool coherent = __any_sync(0xffffffffu, lane < 31 && next == cell);
+    int r;
+    if (coherent) {
+        const unsigned peers = __match_any_sync(0xffffffffu, cell);
+        const int leader = __ffs(peers) - 1;
+        const int within = __popc(peers & ((1u << lane) - 1u));
+        int base = 0;
+        if (valid && lane == leader) base = atomicAdd(counters + cell, __popc(peers));
+        base = __shfl_sync(0xffffffffu, base, leader);
+        r = base + within;
+    } else {
+        r = valid ? atomicAdd(counters + cell, 1) : 0;
+    }
     if (valid) {
         cellid[first + tid] = cell;
-        rank[first + tid] = base + within;
+        rank[first + tid] = r;
     }
 }
 
@@ -268,19 +279,116 @@ kn_order_big_kernel(const int *big_count, const int *__restrict__ big_list, cons
     }
 }
 
+// ------------------------------------------------------------------------------------------ bins
+// Large clouds arrive in random order, so the histogram atomics, the pointer reads of the scatter and
+// the record reads of the gather each touch a random DRAM sector per point (13.4 ms for 100 M points).
+// One coalesced pre-pass removes that: a STABLE split of the input into kBins z-bands of planes, written
+// as 16-byte records (x, y, z, input index).  All later random accesses of a band then stay inside a few
+// tens of MB -- L2-resident on B200 (126 MB) -- and the build drops to ~1/3 (profiles/r1_notes.md).
+// Stable (input order kept inside a band), so "ascending record position" inside a cell is still
+// "ascending original index" and the layout stays the deterministic stable counting sort.
+constexpr int kBins = 64;
+constexpr int kBinThreads = 1024;
+
+__device__ __forceinline__ int bin_of(const float *rec, const GridGeom &g, int planes_per_bin) {
+    return (axis_cell(__ldg(rec + 2), g.Df, g.zb, g.ze - 1) - g.zb) / planes_per_bin;
+}
+
+// rank of this thread among the block's earlier threads of the same bin, and the block's bin counts
+__device__ __forceinline__ int bin_rank_in_block(int bin, bool valid, int (*s_cnt)[kBins]) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < (kBinThreads / 32) * kBins; i += kBinThreads) (&s_cnt[0][0])[i] = 0;
+    __syncthreads();
+    const unsigned peers = __match_any_sync(0xffffffffu, valid ? bin : -1 - lane);
+    if (valid && lane == __ffs(peers) - 1) s_cnt[warp][bin] = __popc(peers);
+    __syncthreads();
+    int before = __popc(peers & ((1u << lane) - 1u));
+    if (valid)
+        for (int wq = 0; wq < warp; ++wq) before += s_cnt[wq][bin];
+    return before;
+}
+
+__global__ void __launch_bounds__(kBinThreads)
+kn_bin_count_kernel(const float *__restrict__ xyz, int stride, int n, GridGeom g, int planes_per_bin, int nblocks,
+                    int *__restrict__ blockcounts) {
+    __shared__ int s_cnt[kBinThreads / 32][kBins];
+    const long long i = (long long)blockIdx.x * kBinThreads + threadIdx.x;
+    const bool valid = i < n;
+    const int bin = valid ? bin_of(xyz + i * stride, g, planes_per_bin) : 0;
+    bin_rank_in_block(bin, valid, s_cnt);
+    if (threadIdx.x < kBins) {
+        int c = 0;
+        for (int wq = 0; wq < kBinThreads / 32; ++wq) c += s_cnt[wq][threadIdx.x];
+        blockcounts[(size_t)threadIdx.x * nblocks + blockIdx.x] = c;
+    }
+}
+
+// one block per bin: exclusive scan of its row of per-block counts (in place), row total to totals[bin]
+__global__ void __launch_bounds__(1024) kn_bin_scan_kernel(int *blockcounts, int nblocks, int *totals) {
+    __shared__ int s_warp[32];
+    __shared__ int s_carry;
+    int *row = blockcounts + (size_t)blockIdx.x * nblocks;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_carry = 0;
+    __syncthreads();
+    for (int base = 0; base < nblocks; base += 1024) {
+        const int idx = base + tid;
+        const int v = idx < nblocks ? row[idx] : 0;
+        int incl = v;
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        int off = s_carry;
+        for (int wq = 0; wq < warp; ++wq) off += s_warp[wq];
+        if (idx < nblocks) row[idx] = off + incl - v;
+        __syncthreads();
+        if (tid == 1023) s_carry = off + incl;
+        __syncthreads();
+    }
+    if (tid == 0) totals[blockIdx.x] = s_carry;
+}
+
+__global__ void __launch_bounds__(kBinThreads)
+kn_bin_scatter_kernel(const float *__restrict__ xyz, int stride, int n, GridGeom g, int planes_per_bin, int nblocks,
+                      const int *__restrict__ offsets, const int *__restrict__ totals, float4 *__restrict__ recs) {
+    __shared__ int s_cnt[kBinThreads / 32][kBins];
+    __shared__ int s_base[kBins];
+    const long long i = (long long)blockIdx.x * kBinThreads + threadIdx.x;
+    const bool valid = i < n;
+    const float *rec = xyz + (valid ? i : 0) * stride;
+    const int bin = valid ? bin_of(rec, g, planes_per_bin) : 0;
+    if (threadIdx.x < kBins) {  // first record of each band: the totals of the lower bands
+        int b = 0;
+        for (int q = 0; q < (int)threadIdx.x; ++q) b += __ldg(totals + q);
+        s_base[threadIdx.x] = b;
+    }
+    const int before = bin_rank_in_block(bin, valid, s_cnt);  // contains the barriers that publish s_base
+    if (valid) {
+        const int pos = s_base[bin] + __ldg(offsets + (size_t)bin * nblocks + blockIdx.x) + before;
+        recs[pos] = make_float4(__ldg(rec), __ldg(rec + 1), __ldg(rec + 2), __uint_as_float((unsigned)i));
+    }
+}
+
 // --------------------------------------------------------------------------------------- gather
 __global__ void __launch_bounds__(kBuildThreads)
-kn_gather_kernel(const float *__restrict__ xyz, int stride, int n, const unsigned int *__restrict__ permutation,
-                 float *__restrict__ points3, float4 *__restrict__ points4) {
+kn_gather_kernel(const float *__restrict__ xyz, int stride, int n, unsigned int *__restrict__ permutation,
+                 float *__restrict__ points3, float4 *__restrict__ points4, int binned) {
     __shared__ float tile[kBuildThreads * 3];
     const int tid = threadIdx.x;
     const long long first = (long long)blockIdx.x * kBuildThreads;
     const long long s = first + tid;
     const int here = (int)min((long long)kBuildThreads, (long long)n - first);
     if (s < n) {
-        const unsigned i = __ldg(permutation + s);
+        unsigned i = permutation[s];
         const float *rec = xyz + (long long)stride * i;
         const float x = __ldg(rec), y = __ldg(rec + 1), z = __ldg(rec + 2);
+        if (binned) {  // `i` was a position in the binned records; their 4th word is the original index
+            i = __float_as_uint(__ldg(rec + 3));
+            permutation[s] = i;
+        }
         points4[s] = make_float4(x, y, z, __uint_as_float(i));
         tile[3 * tid] = x; tile[3 * tid + 1] = y; tile[3 * tid + 2] = z;
     }
@@ -331,8 +439,22 @@ cudaError_t kn_launch_build(const float *d_in_xyz, int stride, int n, const Grid
     if ((e = cudaMemsetAsync(d_counters, 0, sizeof(int) * (size_t)cells, st)) != cudaSuccess) return e;
     if ((e = cudaMemsetAsync(s.d_tile, 0, sizeof(unsigned long long) * s.tile_count, st)) != cudaSuccess) return e;
     if ((e = cudaMemsetAsync(s.d_ticket, 0, sizeof(int) * 2, st)) != cudaSuccess) return e;
-    const int aligned16 = ((uintptr_t)d_in_xyz & 15u) == 0;
-    kn_count_kernel<<<blocks_for(n, kBuildThreads), kBuildThreads, 0, st>>>(d_in_xyz, stride, n, g, d_counters,
+    const float *src = d_in_xyz;
+    int binned = 0;
+    if (s.d_bin_recs) {  // large cloud: stable split into z-bands first (see "bins" above)
+        const int planes = g.ze - g.zb;
+        const int planes_per_bin = (planes + kBins - 1) / kBins;
+        const int nblocks = (int)blocks_for(n, kBinThreads);
+        kn_bin_count_kernel<<<nblocks, kBinThreads, 0, st>>>(d_in_xyz, stride, n, g, planes_per_bin, nblocks, s.d_bin_counts);
+        kn_bin_scan_kernel<<<kBins, 1024, 0, st>>>(s.d_bin_counts, nblocks, s.d_bin_counts + (size_t)kBins * nblocks);
+        kn_bin_scatter_kernel<<<nblocks, kBinThreads, 0, st>>>(d_in_xyz, stride, n, g, planes_per_bin, nblocks, s.d_bin_counts,
+                                                              s.d_bin_counts + (size_t)kBins * nblocks, s.d_bin_recs);
+        src = reinterpret_cast<const float *>(s.d_bin_recs);
+        stride = 4;
+        binned = 1;
+    }
+    const int aligned16 = ((uintptr_t)src & 15u) == 0;
+    kn_count_kernel<<<blocks_for(n, kBuildThreads), kBuildThreads, 0, st>>>(src, stride, n, g, d_counters,
                                                                            s.d_cellid, s.d_rank, aligned16);
     kn_scan_kernel<<<(unsigned)s.tile_count, kBuildThreads, 0, st>>>(d_counters, d_ptrs, cells, s.d_tile,
                                                                     s.d_ticket, d_globcounter);
@@ -341,10 +463,12 @@ cudaError_t kn_launch_build(const float *d_in_xyz, int stride, int n, const Grid
     kn_order_kernel<<<blocks_for(cells, kBuildThreads), kBuildThreads, 0, st>>>(cells, d_ptrs, d_permutation,
                                                                                s.d_ticket + 1, s.d_biglist);
     kn_order_big_kernel<<<148, 1024, 0, st>>>(s.d_ticket + 1, s.d_biglist, d_ptrs, d_permutation);
-    kn_gather_kernel<<<blocks_for(n, kBuildThreads), kBuildThreads, 0, st>>>(d_in_xyz, stride, n, d_permutation,
-                                                                            d_points3, d_points4);
+    kn_gather_kernel<<<blocks_for(n, kBuildThreads), kBuildThreads, 0, st>>>(src, stride, n, d_permutation,
+                                                                            d_points3, d_points4, binned);
     return cudaGetLastError();
 }
+
+size_t kn_bin_counts_ints(int n) { return (size_t)kBins * blocks_for(n, kBinThreads) + kBins; }
 
 cudaError_t kn_launch_generate(float *d_xyz, long long first, long long count, uint64_t seed, cudaStream_t st) {
     const long long count3 = count * 3;

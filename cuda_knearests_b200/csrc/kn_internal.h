@@ -47,7 +47,11 @@ struct BuildScratch {
     int *d_ticket;               // scan ticket + big-cell worklist counter
     int *d_biglist;              // [n / KN_BIG_CELL + 1] cells too large for the per-thread ordering
     size_t tile_count;
+    float4 *d_bin_recs;          // [n] z-banded copy of the input (large clouds only, else NULL)
+    int *d_bin_counts;           // [kn_bin_counts_ints(n)] per-block band counts + band totals
 };
+size_t kn_bin_counts_ints(int n);
+#define KN_BIN_MIN_POINTS 4000000  // below this the histogram stays in L2 anyway
 size_t kn_build_scratch_tiles(long long cells);
 cudaError_t kn_launch_build(const float *d_in_xyz, int stride, int n, const GridGeom &g, long long cells, int *d_counters,
                             int *d_ptrs, int *d_globcounter, unsigned int *d_permutation, float *d_points3,

@@ -56,7 +56,8 @@ typedef struct {
     int own_z_begin, own_z_end;
     float search_scale;     /* tuning: multiplies the first-guess search radius; default 1             */
     int algorithm;          /* 0 = automatic (select/insertion kernel + retry), 1 = general kernel only,
-                               2 = insertion kernel for every k (testing, A/B)                          */
+                               2 = insertion kernel for every k, 3 = grid build without the z-band
+                               pre-pass (testing, A/B)                                                  */
     int point_stride;       /* floats per input point: 3 (xyz, default) or 4 (xyz + one ignored word,
                                e.g. the records knc_slab_route writes)                                  */
 } knc_options;

@@ -89,6 +89,19 @@ def test_search_radius_guess_does_not_change_rows(kn, oracle):
         assert np.array_equal(r["knn"], want), scale
 
 
+def test_large_cloud_banded_build_is_the_same_stable_sort(kn, oracle):
+    """From 4 M points on, the build first splits the input into z-bands (L2 locality); the layout must
+    still be the deterministic stable counting sort, and identical to the build without the pre-pass."""
+    n = 5_000_000
+    pts = oracle.generate_uniform(n, seed=99)
+    r = run_engine(kn, pts, 8)
+    g = assert_layout_equals_oracle(oracle, pts, r)
+    assert np.array_equal(r["knn"], g.knn_exact(8))
+    plain = run_engine(kn, pts, 8, algorithm=3)  # no z-band pre-pass
+    for key in ("knn", "perm", "points"):
+        assert np.array_equal(r[key], plain[key])
+
+
 def test_device_input_equals_host_input(kn, oracle):
     import torch
     n = 250_000
