@@ -1,0 +1,47 @@
+"""The drop-in boundary at the C++ level: a caller written against the reference's interface only
+(tests/cpp/dropin_main.cu: params.h + knearests.h, the reference driver's call sequence) is compiled with
+nvcc, linked against libknearests_b200.so and run on the reference's fixture.  Its output must be the
+oracle's rows.  __graft_entry__.build() compiles the binary; the test compiles it itself if it is missing."""
+import subprocess
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+ROOT = Path(__file__).resolve().parent.parent
+BIN = ROOT / "tests" / "cpp" / "dropin_test"
+
+
+def build_dropin():
+    lib = ROOT / "cuda_knearests_b200"
+    subprocess.run(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-O2", f"-I{ROOT / 'include'}",
+                    str(ROOT / "tests" / "cpp" / "dropin_main.cu"), "-o", str(BIN), f"-L{lib}", "-lknearests_b200",
+                    "-Xlinker", f"-rpath={lib}"], check=True)
+
+
+def test_dropin_binary_links_against_the_reference_symbols():
+    """No GPU needed: the caller's undefined symbols are the reference's mangled names, and they resolve."""
+    if not BIN.exists():
+        build_dropin()
+    out = subprocess.run(["nm", "-u", str(BIN)], capture_output=True, text=True, check=True).stdout
+    for sym in ("_Z10kn_prepareP6float3i", "_Z8kn_solveP10kn_problem", "_Z16kn_get_knearestsP10kn_problem",
+                "_Z18kn_get_permutationP10kn_problem", "_Z13kn_get_pointsP10kn_problem",
+                "_Z14kn_print_statsP10kn_problem", "_Z7kn_freePP10kn_problem"):
+        assert sym in out
+
+
+@pytest.mark.gpu
+def test_dropin_caller_gets_the_oracle_rows(oracle, pts20k, tmp_path):
+    if not BIN.exists():
+        build_dropin()
+    pts20k.tofile(tmp_path / "points.f32")
+    r = subprocess.run([str(BIN), str(tmp_path / "points.f32"), str(tmp_path / "neighbors.u32")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    assert "Grid:  points per cell: 0 (min), 8 (max)" in r.stderr  # kn_print_stats, as the reference prints it
+    assert "[3] => 2091" in r.stderr
+    got = np.fromfile(tmp_path / "neighbors.u32", np.uint32).reshape(-1, 50)
+    g = oracle.Grid(pts20k)
+    want = np.empty_like(got)
+    want[g.permutation] = g.permutation[g.knn_exact(50)]
+    assert np.array_equal(got, want)
