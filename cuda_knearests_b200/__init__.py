@@ -29,6 +29,7 @@ C_ABI_SYMBOLS = [
     "knc_get_knearests", "knc_get_knearests_original", "knc_get_stats", "knc_get_info", "knc_get_timings",
     "knc_grid_dim", "knc_last_error", "knc_version", "knc_generate_uniform_device", "knc_scan_cells_noalloc",
     "knc_slab_route", "knc_get_knearests_global", "knc_set_index_offset", "knc_get_permutation_global",
+    "knc_get_dists", "knc_query_points",
 ]
 # the reference's own (C++-mangled) entry points, knearests.h:21-29
 CXX_ABI_SYMBOLS = [
@@ -95,6 +96,8 @@ def lib() -> C.CDLL:
         for nm in ("knc_get_points", "knc_get_permutation", "knc_get_knearests", "knc_get_knearests_original"):
             getattr(L, nm).argtypes = [vp, vp]
         L.knc_solve_to_host.argtypes = [vp, vp, C.c_int]
+        L.knc_get_dists.argtypes = [vp, vp]
+        L.knc_query_points.argtypes = [vp, vp, C.c_int, vp, vp]
         L.knc_get_stats.argtypes = [vp, C.POINTER(Stats)]
         L.knc_get_info.argtypes = [vp, C.POINTER(Info)]
         L.knc_get_timings.argtypes = [vp, C.POINTER(Timings)]
@@ -178,6 +181,21 @@ class KnProblem:
         _check(lib().knc_solve_to_host(self._h, out.ctypes.data, int(chunks)))
         self.info = self._info()
         return out
+
+    def get_dists(self) -> np.ndarray:
+        """Squared distances of the rows (the reference's GPU API returns none; its kd-tree does)."""
+        out = np.empty((self.info.query_count, self.info.k), np.float32)
+        _check(lib().knc_get_dists(self._h, out.ctypes.data))
+        return out
+
+    def query_points(self, xyz, with_d2: bool = False):
+        """kNN of points that are not in the cloud (kd_tree.cpp:168-192 semantics)."""
+        q = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        rows = np.empty((q.shape[0], self.info.k), np.uint32)
+        d2 = np.empty((q.shape[0], self.info.k), np.float32) if with_d2 else None
+        _check(lib().knc_query_points(self._h, q.ctypes.data, q.shape[0], rows.ctypes.data,
+                                      d2.ctypes.data if with_d2 else None))
+        return (rows, d2) if with_d2 else rows
 
     def get_points(self) -> np.ndarray:  # kn_get_points, knearests.cu:410
         out = np.empty((self.info.n, 3), np.float32)

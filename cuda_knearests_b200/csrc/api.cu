@@ -305,7 +305,7 @@ static int solve_impl(knc_problem *p, unsigned int *out_knn_host, int chunks, co
         unsigned int *rows = p->pub.d_knearests + (size_t)q0 * p->k;
         if (c) CU(cudaMemsetAsync(p->d_diag + 3, 0, sizeof(unsigned), st));  // the retry list starts empty
         CU(kn_launch_query(p->d_points4, p->pub.d_ptrs, g, p->pub.allocated_points, p->k, p->query_begin + q0, qn,
-                           (float)(r0 * r0), rows, p->d_diag, d_retry, force_general, p->index_offset, st));
+                           (float)(r0 * r0), rows, p->d_diag, d_retry, force_general, p->index_offset, NULL, st));
         if (out_knn_host) {
             CU(cudaEventCreateWithFlags(&done[made], cudaEventDisableTiming));
             ++made;
@@ -343,6 +343,71 @@ int knc_solve(knc_problem *p) { return solve_impl(p, NULL, 1, "knc_solve"); }
 int knc_solve_to_host(knc_problem *p, unsigned int *out_knn, int chunks) {
     if (!out_knn) return fail(KNC_ERR_INVALID, "knc_solve_to_host: out_knn is NULL");
     return solve_impl(p, out_knn, chunks > 0 ? chunks : 8, "knc_solve_to_host");
+}
+
+static double first_radius(const knc_problem *p) {
+    const double volume = 1000.0 * 1000.0 * (1000.0 * (p->z_end - p->z_begin) / p->dim_global);
+    const double rho = (double)p->pub.allocated_points / volume;
+    const double lambda = p->k + 2.5 * sqrt((double)p->k) + 2.0;
+    return cbrt(3.0 * lambda / (4.0 * M_PI * rho)) * p->search_scale;
+}
+
+int knc_get_dists(knc_problem *p, float *out_d2) {
+    int rc = KNC_OK;
+    float *d_out = NULL;
+    if (!p || !out_d2) return fail(KNC_ERR_INVALID, "knc_get_dists: NULL argument");
+    if (!p->solved) return fail(KNC_ERR_STATE, "knc_get_dists: call knc_solve first");
+    {
+        const size_t bytes = sizeof(float) * (size_t)p->query_count * p->k;
+        CU(dev_alloc((void **)&d_out, bytes, p->stream));
+        CU(kn_launch_rows_dists(p->d_points4, p->pub.d_knearests, NULL, p->query_begin, p->index_offset, p->query_count,
+                                p->k, d_out, p->stream));
+        CU(cudaMemcpyAsync(out_d2, d_out, bytes, cudaMemcpyDeviceToHost, p->stream));
+        CU(cudaStreamSynchronize(p->stream));
+    }
+out:
+    if (d_out) cudaFreeAsync(d_out, p->stream);
+    return rc;
+}
+
+int knc_query_points(knc_problem *p, const float *xyz, int m, unsigned int *out_knn, float *out_d2) {
+    int rc = KNC_OK;
+    float *d_q = NULL, *d_d2 = NULL;
+    unsigned *d_rows = NULL, *d_diag = NULL;
+    unsigned diag[4] = {0, 0, 0, 0};
+    if (!p || !xyz || !out_knn || m < 1) return fail(KNC_ERR_INVALID, "knc_query_points: bad argument");
+    {
+        cudaStream_t st = p->stream;
+        GridGeom g;
+        const int D = p->dim_global;
+        g.D = D; g.zb = p->z_begin; g.ze = p->z_end; g.Df = (float)D; g.w = 1000.f / (float)D; g.invw = (float)D / 1000.f;
+        const double r0 = first_radius(p);
+        const size_t rows_bytes = sizeof(unsigned) * (size_t)m * p->k;
+        CU(dev_alloc((void **)&d_q, sizeof(float) * 3 * (size_t)m, st));
+        CU(dev_alloc((void **)&d_rows, rows_bytes, st));
+        CU(dev_alloc((void **)&d_diag, sizeof(unsigned) * 4, st));
+        CU(cudaMemcpyAsync(d_q, xyz, sizeof(float) * 3 * (size_t)m, cudaMemcpyHostToDevice, st));
+        CU(cudaMemsetAsync(d_diag, 0, sizeof(unsigned) * 4, st));
+        CU(kn_launch_query(p->d_points4, p->pub.d_ptrs, g, p->pub.allocated_points, p->k, 0, m, (float)(r0 * r0), d_rows,
+                           d_diag, NULL, 1, p->index_offset, d_q, st));
+        CU(cudaMemcpyAsync(out_knn, d_rows, rows_bytes, cudaMemcpyDeviceToHost, st));
+        CU(cudaMemcpyAsync(diag, d_diag, sizeof(diag), cudaMemcpyDeviceToHost, st));
+        if (out_d2) {
+            CU(dev_alloc((void **)&d_d2, sizeof(float) * (size_t)m * p->k, st));
+            CU(kn_launch_rows_dists(p->d_points4, d_rows, d_q, 0, p->index_offset, m, p->k, d_d2, st));
+            CU(cudaMemcpyAsync(out_d2, d_d2, sizeof(float) * (size_t)m * p->k, cudaMemcpyDeviceToHost, st));
+        }
+        CU(cudaStreamSynchronize(st));
+        if (diag[2])
+            rc = fail(KNC_ERR_HALO, "knc_query_points: %u queries reach beyond the planes [%d,%d) of this slab", diag[2],
+                      p->z_begin, p->z_end);
+    }
+out:
+    if (d_q) cudaFreeAsync(d_q, p->stream);
+    if (d_rows) cudaFreeAsync(d_rows, p->stream);
+    if (d_d2) cudaFreeAsync(d_d2, p->stream);
+    if (d_diag) cudaFreeAsync(d_diag, p->stream);
+    return rc;
 }
 
 int knc_set_index_offset(knc_problem *p, long long offset) {

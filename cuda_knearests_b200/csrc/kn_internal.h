@@ -64,7 +64,10 @@ cudaError_t kn_launch_remap_original(const unsigned int *d_knn, const unsigned i
 cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const GridGeom &g, int n, int k,
                             int query_begin, int query_count, float radius0_sq, unsigned int *d_knn,
                             unsigned int *d_diag, int *d_retry_list, int force_general, unsigned int index_offset,
-                            cudaStream_t st);
+                            const float *d_ext_queries, cudaStream_t st);
+cudaError_t kn_launch_rows_dists(const float4 *d_points4, const unsigned int *d_rows, const float *d_ext_queries,
+                                 int query_begin, unsigned int index_offset, long long rows, int k, float *d_out,
+                                 cudaStream_t st);
 
 // ---- api.cu ------------------------------------------------------------------------------------
 int kn_set_error(int code, const char *fmt, ...);  // records the message knc_last_error() returns

@@ -78,6 +78,7 @@ struct QueryParams {
     float radius0_sq;
     int use_select;        // small k: remember-then-select kernel instead of the insertion kernel
     unsigned index_offset; // added to every stored neighbour index (slab mode: local -> global sorted position)
+    const float *ext_queries;  // EXTERNAL mode of the general kernel: query points that are not in the cloud (xyz)
     int *retry_list;       // sorted positions of the queries the fast kernel could not finish
     unsigned int *retry_count;
     RowTable tab;
@@ -540,10 +541,12 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
 
 // ===================================================================================== general path
 // Per-lane nested loops over rows and candidates, restarts with a growing radius, plain square rings
-// of rows beyond the table: exact for any input.  RETRY = false: one thread per query of the range
-// (used when the fast path does not apply); RETRY = true: the queries listed by the fast kernel.
-template <int K_T, int QB, bool RETRY>
+// of rows beyond the table: exact for any input.  MODE 0: one thread per query of the range (used when
+// the fast path does not apply); MODE 1 (RETRY): the queries listed by the fast kernel; MODE 2
+// (EXTERNAL): query points that are not members of the cloud (P.ext_queries), nothing excluded.
+template <int K_T, int QB, int MODE>
 __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_constant__ QueryParams P) {
+    constexpr bool RETRY = MODE == 1, EXTERNAL = MODE == 2;
     extern __shared__ unsigned long long smem[];  // [K][QB]: slot-major, thread-minor
     const int K = K_T ? K_T : P.k;
     const int tid = threadIdx.x;
@@ -558,8 +561,10 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
         const bool valid = row0 + tid < total;
         const long long slot = min(row0 + tid, total - 1);
         const int entry = RETRY ? P.retry_list[slot] : P.query_begin + (int)slot;
-        const int q = entry & 0x7FFFFFFF;
-        const QueryGeom s = query_geom(__ldg(P.pts + q), P.g);
+        const int q = EXTERNAL ? -1 : (entry & 0x7FFFFFFF);  // -1: no candidate position equals it, nothing is excluded
+        const QueryGeom s = EXTERNAL ? query_geom(make_float4(__ldg(P.ext_queries + 3 * slot), __ldg(P.ext_queries + 3 * slot + 1),
+                                                              __ldg(P.ext_queries + 3 * slot + 2), 0.f), P.g)
+                                     : query_geom(__ldg(P.pts + q), P.g);
 
         int cnt = 0;
         unsigned long long kth = ~0ull;
@@ -659,6 +664,13 @@ cudaError_t launch(const QueryParams &P, bool fast, cudaStream_t st) {
     const size_t list_bytes = sizeof(unsigned long long) * (size_t)P.k * QB;
     const unsigned blocks = (unsigned)(((long long)P.query_count + QB - 1) / QB);
     cudaError_t e;
+    if (P.ext_queries) {
+        e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)list_bytes);
+        if (e != cudaSuccess) return e;
+        kn_query_general_kernel<K_T, QB, 2><<<blocks, QB, list_bytes, st>>>(P);
+        return cudaGetLastError();
+    }
     constexpr bool kHasSelect = K_T == 8 || K_T == 20 || K_T == 32 || K_T == 50;
     if (fast && kHasSelect && P.use_select) {
         if constexpr (kHasSelect) {
@@ -669,26 +681,26 @@ cudaError_t launch(const QueryParams &P, bool fast, cudaStream_t st) {
             if (e != cudaSuccess) return e;
             kn_query_select_kernel<K_T, QB, NET, CAP><<<blocks, QB, smem, st>>>(P);
         }
-        e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)list_bytes);
         if (e != cudaSuccess) return e;
         const unsigned retry_blocks = blocks < 148u * 8u ? blocks : 148u * 8u;
-        kn_query_general_kernel<K_T, QB, true><<<retry_blocks, QB, list_bytes, st>>>(P);
+        kn_query_general_kernel<K_T, QB, 1><<<retry_blocks, QB, list_bytes, st>>>(P);
     } else if (fast) {
         const size_t smem = list_bytes + sizeof(unsigned long long) * (size_t)(kSpanSlots + kQueueSlots) * QB;
         e = cudaFuncSetAttribute(kn_query_fast_kernel<K_T, QB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         kn_query_fast_kernel<K_T, QB><<<blocks, QB, smem, st>>>(P);
-        e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)list_bytes);
         if (e != cudaSuccess) return e;
         const unsigned retry_blocks = blocks < 148u * 8u ? blocks : 148u * 8u;  // loops over the retry list
-        kn_query_general_kernel<K_T, QB, true><<<retry_blocks, QB, list_bytes, st>>>(P);
+        kn_query_general_kernel<K_T, QB, 1><<<retry_blocks, QB, list_bytes, st>>>(P);
     } else {
-        e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)list_bytes);
         if (e != cudaSuccess) return e;
-        kn_query_general_kernel<K_T, QB, false><<<blocks, QB, list_bytes, st>>>(P);
+        kn_query_general_kernel<K_T, QB, 0><<<blocks, QB, list_bytes, st>>>(P);
     }
     return cudaGetLastError();
 }
@@ -727,7 +739,7 @@ void fill_table(RowTable &t, float w) {
 cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const GridGeom &g, int n, int k,
                             int query_begin, int query_count, float radius0_sq, unsigned int *d_knn,
                             unsigned int *d_diag, int *d_retry_list, int force_general, unsigned int index_offset,
-                            cudaStream_t st) {
+                            const float *d_ext_queries, cudaStream_t st) {
     if (query_count <= 0) return cudaSuccess;
     QueryParams P;
     P.pts = d_points4; P.ptrs = d_ptrs; P.knn = d_knn; P.diag = d_diag; P.g = g;
@@ -735,6 +747,7 @@ cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const Gr
     P.radius0_sq = radius0_sq;
     P.retry_list = d_retry_list;
     P.index_offset = index_offset;
+    P.ext_queries = d_ext_queries;
     P.use_select = force_general != 2;  // algorithm 2 = insertion kernel even for small k (A/B, tests)
     P.retry_count = d_diag + 3;
     fill_table(P.tab, g.w);
@@ -752,4 +765,37 @@ cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const Gr
     if (k <= 96) return launch<0, 128>(P, fast, st);
     if (k <= 192) return launch<0, 64>(P, fast, st);
     return launch<0, 32>(P, fast, st);
+}
+
+// d2 of every stored row entry, with the reference's expression (knearests.cu:125 as compiled) -- the reference
+// never returns distances; this recomputes them from the rows.
+namespace {
+__global__ void kn_rows_dists_kernel(const float4 *__restrict__ pts, const unsigned *__restrict__ rows,
+                                     const float *__restrict__ ext_queries, int query_begin, unsigned index_offset,
+                                     long long total, int k, float *__restrict__ out) {
+    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= total) return;
+    const long long r = e / k;
+    const unsigned v = __ldg(rows + e);
+    float d2 = FLT_MAX;
+    if (v != KNC_EMPTY) {
+        float qx, qy, qz;
+        if (ext_queries) { qx = __ldg(ext_queries + 3 * r); qy = __ldg(ext_queries + 3 * r + 1); qz = __ldg(ext_queries + 3 * r + 2); }
+        else { const float4 q = __ldg(pts + query_begin + r); qx = q.x; qy = q.y; qz = q.z; }
+        const float4 c = __ldg(pts + (v - index_offset));
+        const float dx = c.x - qx, dy = c.y - qy, dz = c.z - qz;
+        d2 = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+    }
+    out[e] = d2;
+}
+}  // namespace
+
+cudaError_t kn_launch_rows_dists(const float4 *d_points4, const unsigned int *d_rows, const float *d_ext_queries,
+                                 int query_begin, unsigned int index_offset, long long rows, int k, float *d_out,
+                                 cudaStream_t st) {
+    const long long total = rows * k;
+    if (total > 0)
+        kn_rows_dists_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d_points4, d_rows, d_ext_queries, query_begin,
+                                                                             index_offset, total, k, d_out);
+    return cudaGetLastError();
 }

@@ -133,6 +133,18 @@ int knc_get_knearests(knc_problem *p, unsigned int *out_knn);
  * Whole-grid handles only (not slab mode).  out: n*k unsigned, host. */
 int knc_get_knearests_original(knc_problem *p, unsigned int *out_neighbors);
 
+/* Squared distances of the stored rows (HOST, query_count*k floats; FLT_MAX where a row entry is KNC_EMPTY),
+ * recomputed with the reference's f32 expression fma(dz,dz, fma(dx,dx, dy*dy)) (knearests.cu:125 as compiled).
+ * The reference API never returns distances (knearests.h:21-29); its kd-tree does
+ * (kd_tree.cpp:168, neighbors_sq_dist). */
+int knc_get_dists(knc_problem *p, float *out_d2);
+
+/* k nearest neighbours of m query points that are NOT members of the cloud (HOST xyz, m*3 floats), as the
+ * reference's kd-tree offers (kd_tree.cpp:168-192: query by coordinates); the reference's GPU path has no such
+ * entry point.  Rows (HOST, m*k unsigned) hold sorted positions, ascending (d2, sorted position), nothing is
+ * excluded; out_d2 (HOST, m*k floats) may be NULL.  Works on any prepared handle, solved or not. */
+int knc_query_points(knc_problem *p, const float *xyz, int m, unsigned int *out_knn, float *out_d2);
+
 /* Replaces kn_print_stats (knearests.h:29, knearests.cu:440-466), as data. */
 int knc_get_stats(knc_problem *p, knc_stats *out);
 

@@ -63,6 +63,8 @@ def lib() -> C.CDLL:
         L.kno_knn_exact.restype = None
         L.kno_brute.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _u32p, C.c_void_p]
         L.kno_brute.restype = None
+        L.kno_brute_external.argtypes = [_f32p, C.c_int, _f32p, C.c_int, C.c_int, _u32p, C.c_void_p]
+        L.kno_brute_external.restype = None
         L.kno_canonical_rows.argtypes = [_u32p, C.c_void_p, _f32p, C.c_int, C.c_int, _u32p, _f32p]
         L.kno_canonical_rows.restype = None
         L.kno_load_xyz.argtypes = [C.c_char_p, _f32p, C.c_int, C.c_int]
@@ -144,6 +146,17 @@ def brute(xyz: np.ndarray, K: int, q0: int = 0, q1: int | None = None, formula: 
     d2 = np.empty((q1 - q0, K), np.float32) if with_d2 else None
     lib().kno_brute(xyz, n, q0, q1, K, 0 if formula == "gpu" else 1, out,
                     d2.ctypes.data if with_d2 else None)
+    return (out, d2) if with_d2 else out
+
+
+def brute_external(xyz: np.ndarray, queries: np.ndarray, K: int, with_d2: bool = False):
+    """K nearest of `xyz` for arbitrary query points (kd_tree.cpp:168-192 semantics), order (d2_gpu, index)."""
+    xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+    queries = np.ascontiguousarray(queries, np.float32).reshape(-1, 3)
+    out = np.empty((queries.shape[0], K), np.uint32)
+    d2 = np.empty((queries.shape[0], K), np.float32) if with_d2 else None
+    lib().kno_brute_external(xyz, xyz.shape[0], queries, queries.shape[0], K, out,
+                             d2.ctypes.data if with_d2 else None)
     return (out, d2) if with_d2 else out
 
 

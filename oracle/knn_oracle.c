@@ -305,6 +305,30 @@ void kno_brute(const float *xyz, int n, int q0, int q1, int K, int formula, unsi
     }
 }
 
+/* Brute force for query points that are NOT members of the cloud (the reference's kd-tree takes an
+ * arbitrary query point, kd_tree.cpp:168-192; its GPU path does not).  K best of all n points under
+ * (d2_gpu, index); nothing is excluded. */
+void kno_brute_external(const float *xyz, int n, const float *queries, int m, int K, unsigned *knn, float *knn_d2) {
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int q = 0; q < m; q++) {
+        kno_ent best[K];
+        int cnt = 0;
+        float px = queries[3 * q], py = queries[3 * q + 1], pz = queries[3 * q + 2];
+        for (int p = 0; p < n; p++) {
+            float d = kno_dist_gpu(xyz[3 * p], xyz[3 * p + 1], xyz[3 * p + 2], px, py, pz);
+            if (cnt == K && !kno_ent_less(d, (unsigned)p, &best[K - 1])) continue;
+            int s = cnt < K ? cnt++ : K - 1;
+            while (s > 0 && kno_ent_less(d, (unsigned)p, &best[s - 1])) { best[s] = best[s - 1]; s--; }
+            best[s].d = d;
+            best[s].p = (unsigned)p;
+        }
+        for (int i = 0; i < K; i++) {
+            knn[(size_t)q * K + i] = i < cnt ? best[i].p : KNO_EMPTY;
+            if (knn_d2) knn_d2[(size_t)q * K + i] = i < cnt ? best[i].d : FLT_MAX;
+        }
+    }
+}
+
 /* ------------------------------------------------------------------------------------------
  * Canonical comparison form (the remap is test_knearests.cu:155-160).
  * in : knn[n*K] rows indexed by sorted position holding sorted positions, permutation[n],

@@ -45,3 +45,31 @@ def test_dropin_caller_gets_the_oracle_rows(oracle, pts20k, tmp_path):
     want = np.empty_like(got)
     want[g.permutation] = g.permutation[g.knn_exact(50)]
     assert np.array_equal(got, want)
+
+
+@pytest.mark.gpu
+def test_cli_driver_loads_xyz_like_the_reference_and_prints_its_lines(oracle, tmp_path):
+    """tools/kn_cli: .xyz in, the reference driver's kind of stderr lines, neighbour table out."""
+    cli = ROOT / "tools" / "kn_cli"
+    if not cli.exists():
+        import __graft_entry__ as G
+        G.build()
+    rng = np.random.default_rng(11)
+    raw = (rng.random((30000, 3)) * [2.0, 1.0, 0.5]).astype(np.float32)
+    xyz = tmp_path / "cloud.xyz"
+    with open(xyz, "w") as f:
+        f.write(f"{len(raw)}\n")
+        for p in raw:
+            f.write(f"{p[0]:.9g} {p[1]:.9g} {p[2]:.9g}\n")
+    r = subprocess.run([str(cli), str(xyz), str(tmp_path / "nb.u32"), str(tmp_path / "pts.f32")],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    for needle in ("bbox [", "kn_firstbuild: ", "kn_solve: ", "Grid:  points per cell:"):
+        assert needle in r.stderr
+    pts = np.fromfile(tmp_path / "pts.f32", np.float32).reshape(-1, 3)
+    assert np.array_equal(pts, oracle.load_xyz(str(xyz)))  # loader == restated reference loader, bit for bit
+    got = np.fromfile(tmp_path / "nb.u32", np.uint32).reshape(-1, 50)
+    g = oracle.Grid(pts)
+    want = np.empty_like(got)
+    want[g.permutation] = g.permutation[g.knn_exact(50)]
+    assert np.array_equal(got, want)

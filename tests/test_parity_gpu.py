@@ -142,6 +142,32 @@ def test_solve_to_host_streams_the_same_rows(kn, oracle):
         assert np.array_equal(p.solve_to_host(), want)      # pageable buffer: same result, no overlap
 
 
+def test_distances_and_external_query_points(kn, oracle):
+    """distances of the rows, and queries that are not data points (what the reference's kd-tree
+    offers, kd_tree.cpp:168-192).  Distances are bit-exact (same f32 expression), rows are exact."""
+    pts = oracle.generate_uniform(80_000, seed=17)
+    g = oracle.Grid(pts)
+    rng = np.random.default_rng(5)
+    with kn.KnProblem(pts, k=20) as p:
+        p.solve()
+        rows, d2 = p.get_knearests(), p.get_dists()
+        want_rows, want_d2 = g.knn_exact(20, with_d2=True)
+        assert np.array_equal(rows, want_rows)
+        assert np.array_equal(d2.view(np.uint32), want_d2.view(np.uint32))
+        q = np.concatenate([rng.random((3000, 3)).astype(np.float32) * 1000,   # anywhere in the domain
+                            g.sorted_xyz[:200] + np.float32(1e-3),               # right next to data points
+                            g.sorted_xyz[200:300],                                # exactly ON data points
+                            np.float32([[-50, 500, 500], [1200, 1200, 1200]])])   # outside the domain
+        got, got_d2 = p.query_points(q, with_d2=True)
+        want, want_q_d2 = oracle.brute_external(g.sorted_xyz, q, 20, with_d2=True)
+        assert np.array_equal(got, want)
+        assert np.array_equal(got_d2.view(np.uint32), want_q_d2.view(np.uint32))
+        assert (got[3200:3300, 0] == np.arange(200, 300)).all()  # a query on a data point finds it at distance 0
+    with kn.KnProblem(pts, k=50) as p:  # works before knc_solve too
+        q = rng.random((500, 3)).astype(np.float32) * 1000
+        assert np.array_equal(p.query_points(q), oracle.brute_external(g.sorted_xyz, q, 50))
+
+
 def test_original_space_remap(kn, oracle):
     pts = oracle.generate_uniform(60_000, seed=4)
     with kn.KnProblem(pts, k=8) as p:
