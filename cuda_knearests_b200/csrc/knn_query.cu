@@ -22,18 +22,21 @@
 //    has been searched.  The reference gives up silently after ring 15 (knearests.cu:137-139).
 //  * All pruning tests are conservative against f32 rounding (MARGIN / SHRINK below): a candidate is
 //    discarded only when its squared distance is provably greater than the current k-th.
-//  * The k best are a sorted list of 64-bit keys (bits(d2) << 32 | sorted position) per thread in
-//    shared memory, slot-major so that a warp's accesses are conflict free.  One unsigned compare
-//    orders by (d2, position): the result is independent of visiting order, i.e. deterministic, and
-//    the row comes out already sorted (the reference needs a heapsort pass, knearests.cu:141).
-//  * Two kernels.  kn_query_fast_kernel does the common case with warp-uniform control flow: every
-//    lane first turns its rows into a list of point spans (uniform loop over the row table), then all
-//    lanes stream their own spans in one flat loop, one candidate per lane per iteration; candidates
-//    that pass the current bound go to a small per-lane queue and are inserted in bursts, when the
-//    whole warp inserts together.  (v1 walked rows and candidates in per-lane nested loops: 9 of 32
-//    lanes active on average, profiles/r1_query_v1_*.)  A query whose first-guess sphere held fewer
-//    than k points is appended to a retry list, and kn_query_general_kernel -- per-lane nested loops,
-//    restarts, rings beyond the table: exact for anything -- finishes those, densely packed.
+//  * Candidates are ordered by the 64-bit key bits(d2) << 32 | sorted position: one unsigned compare gives the
+//    total order (d2, position), so the result does not depend on visiting order -- deterministic, and
+//    identical across the three kernels below, across grid densities and across GPUs.
+//  * Three kernels (details at each):
+//      kn_query_select_kernel   k = 8 / 20 / 32 / 50.  Warp-uniform control flow: span lists, lock-step
+//                               streaming of the records through two register buffers, candidates inside the
+//                               sphere are only remembered; one sort-select at the end on 32-bit truncated keys
+//                               (Batcher network in registers) with an exactness guard.
+//      kn_query_fast_kernel     other k: same streaming, candidates are merged into a sorted list of 64-bit keys
+//                               in shared memory in warp-wide bursts.
+//      kn_query_general_kernel  per-lane nested loops, restarts, rings beyond the row table: exact for any input;
+//                               finishes the few queries the other two hand over (retry list), densely packed,
+//                               serves clouds whose first radius exceeds the table, and external query points.
+//    (v1 walked rows and candidates in per-lane nested loops for every query: 9 of 32 lanes active on average,
+//    profiles/r1_query_v1_*; the select kernel runs at 31.6.)
 //  * Rows are written through shared memory as one contiguous, coalesced run per block
 //    (the reference writes stride-k, knearests.cu:144-147).
 //
