@@ -48,7 +48,7 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=100_000_000)
+    ap.add_argument("--n", "--points", dest="n", type=int, default=100_000_000)  # --points: torchrun chokes on "--n"
     ap.add_argument("--k", type=int, default=20)
     ap.add_argument("--cpu-sample", type=int, default=16_000_000, help="points of the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
