@@ -222,6 +222,18 @@ def test_points_outside_the_unit_range_are_clamped(kn, oracle):
     assert np.array_equal(r["knn"], g.knn_exact(20))
 
 
+def test_presorted_and_repeated_input_takes_the_aggregated_atomics(kn, oracle):
+    """Input that is already in cell order (every warp of the count kernel sees runs of equal cells: the
+    warp-aggregated atomic path) and input with long runs of one repeated point."""
+    base = oracle.generate_uniform(120_000, seed=23)
+    g0 = oracle.Grid(base)
+    for pts in (np.ascontiguousarray(g0.sorted_xyz),                      # cell-ordered input
+                np.ascontiguousarray(np.repeat(base[:3000], 40, axis=0))):  # 40 copies of each point, adjacent
+        r = run_engine(kn, pts, 8)
+        g = assert_layout_equals_oracle(oracle, pts, r)
+        assert np.array_equal(r["knn"], g.knn_exact(8))
+
+
 def test_clustered_cloud_overfull_cells_and_restarts(kn, oracle):
     # far from uniform: most of the cloud in two tiny blobs (cells with thousands of points -> the
     # block-wide ordering path of the build), the rest sparse (radius guess far too small -> restarts)
