@@ -39,7 +39,7 @@ sys.path.insert(0, str(ROOT))
 SEED = 20171004
 METRIC = "kNN queries/sec"
 UNIT = "queries/s"
-KERNELS_PER_STEP = 8  # count, scan, scatter, order, order_big, gather, query (fast), query (retry)
+KERNELS_PER_STEP = 11  # z-band split (3), count, scan, scatter, order, order_big, gather, query (select), query (retry)
 
 
 def parse():

@@ -291,7 +291,7 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
         line = {"metric": METRIC, "value": n / (wall / args.steps), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
-                "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 12 * args.steps * world,  # per rank: route 3, build 6, query 2, permutation slice 1
+                "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 15 * args.steps * world,  # per rank: route 3, build 6 (+3 z-band split when the slab is large), query 2, permutation slice 1
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": None, "kernel": "kn_query_select_kernel (slowest rank)",
                              "kernel_ms": float(allstats[worst][0].item()),
