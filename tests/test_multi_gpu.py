@@ -29,7 +29,7 @@ def test_route_kernel_is_the_stable_multisplit(kn, oracle):
 
 
 @pytest.mark.parametrize("world,k,n", [(2, 20, 400_000), (4, 8, 600_000), (8, 20, 1_000_000), (3, 50, 300_000),
-                                       (2, 8, 9_000_000)])  # last: slabs big enough for the z-band pre-pass
+                                       (2, 8, 42_000_000)])  # last: slabs big enough for the z-band pre-pass
 def test_emulated_ranks_reproduce_single_gpu_rows(kn, oracle, world, k, n):
     """Rows in GLOBAL sorted positions + permutation slices of the ranks, concatenated, are exactly the
     single-GPU kn_get_knearests / kn_get_permutation arrays; and the same rows in original ids
@@ -37,7 +37,7 @@ def test_emulated_ranks_reproduce_single_gpu_rows(kn, oracle, world, k, n):
     import torch
     from cuda_knearests_b200 import slabs
     pts = oracle.generate_uniform(n, seed=20171004)
-    with kn.KnProblem(pts, k=k, algorithm=3 if n > 4_000_000 else 0) as p:  # big case: reference rows without the pre-pass
+    with kn.KnProblem(pts, k=k, algorithm=3 if n > 20_000_000 else 0) as p:  # big case: reference rows without the pre-pass
         p.solve()
         want_rows, want_perm, want_orig = p.get_knearests(), p.get_permutation(), p.get_knearests_original()
     D, zsplit = slabs.grid_and_split(n, world)

@@ -90,9 +90,9 @@ def test_search_radius_guess_does_not_change_rows(kn, oracle):
 
 
 def test_large_cloud_banded_build_is_the_same_stable_sort(kn, oracle):
-    """From 4 M points on, the build first splits the input into z-bands (L2 locality); the layout must
+    """From 20 M points on, the build first splits the input into z-bands (L2 locality); the layout must
     still be the deterministic stable counting sort, and identical to the build without the pre-pass."""
-    n = 5_000_000
+    n = 21_000_000
     pts = oracle.generate_uniform(n, seed=99)
     r = run_engine(kn, pts, 8)
     g = assert_layout_equals_oracle(oracle, pts, r)
