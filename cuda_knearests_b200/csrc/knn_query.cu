@@ -529,16 +529,19 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
     unsigned res[K_T];
 #pragma unroll
     for (int u = 0; u < K_T; ++u) res[u] = exact ? BUF[(a[u] & kSlotMask) * QB] + P.index_offset : KNC_EMPTY;
+    // Row stride QB + 1: the transposed read below (consecutive threads walk along a row's k entries, i.e.
+    // down a column of OUT) would otherwise hit one bank 16 times over (370 of 2600 L1 wavefronts per warp,
+    // profiles/r1_notes.md).
     __syncthreads();
     unsigned int *OUT = reinterpret_cast<unsigned int *>(smem);
 #pragma unroll
-    for (int u = 0; u < K_T; ++u) OUT[u * QB + tid] = res[u];
+    for (int u = 0; u < K_T; ++u) OUT[u * (QB + 1) + tid] = res[u];
     __syncthreads();
     const int rows = (int)min((long long)QB, (long long)P.query_count - row0);
     unsigned int *out = P.knn + row0 * K_T;
     for (int idx = tid; idx < rows * K_T; idx += QB) {
         const int t = idx / K_T, sl = idx - t * K_T;
-        out[idx] = OUT[sl * QB + t];
+        out[idx] = OUT[sl * (QB + 1) + t];
     }
 }
 
