@@ -115,10 +115,19 @@ __device__ __forceinline__ QueryGeom query_geom(const float4 me, const GridGeom 
     return s;
 }
 
-// Conservative squared distance from the query to the x-row (cj+dj, ck+dk) of cells.
-__device__ __forceinline__ float row_lower_bound2(const QueryGeom &s, int dj, int dk, float w) {
-    const float gy = fmaxf(0.f, fmaxf((float)dj - s.fy, s.fy - (float)dj - 1.f));
-    const float gz = fmaxf(0.f, fmaxf((float)dk - s.fz, s.fz - (float)dk - 1.f));
+// Conservative squared distance from the query to the x-row (j, k) = (cj+dj, ck+dk) of cells.
+// A border cell also holds the points that lie OUTSIDE the domain on its side (cellFromPoint clamps,
+// knearests.cu:26-28), so towards that side the cell is unbounded: no gap may be claimed there.  (It
+// matters when the query itself is outside the domain: its own border row then holds points that are
+// closer to it than the nominal cell box is.)
+__device__ __forceinline__ float row_lower_bound2(const QueryGeom &s, int dj, int dk, float w, const GridGeom &g) {
+    const int j = s.cj + dj, k = s.ck + dk;
+    const float below_y = j > 0 ? (float)dj - s.fy : 0.f;            // query below the row (row's low side bounded)
+    const float above_y = j < g.D - 1 ? s.fy - (float)dj - 1.f : 0.f;  // query above the row
+    const float below_z = k > g.zb ? (float)dk - s.fz : 0.f;
+    const float above_z = k < g.ze - 1 ? s.fz - (float)dk - 1.f : 0.f;
+    const float gy = fmaxf(0.f, fmaxf(below_y, above_y));
+    const float gz = fmaxf(0.f, fmaxf(below_z, above_z));
     const float ly = fmaxf(0.f, fmaf(gy, w, -kMargin)), lz = fmaxf(0.f, fmaf(gz, w, -kMargin));
     return (ly * ly + lz * lz) * kShrink;
 }
@@ -127,8 +136,9 @@ __device__ __forceinline__ float row_lower_bound2(const QueryGeom &s, int dj, in
 __device__ __forceinline__ void row_x_range(const QueryGeom &s, float bound2, float lbyz2, float invw, int D,
                                             int &ilo, int &ihi) {
     const float rxc = fmaf(sqrt_approx(bound2 - lbyz2) * kGrow, invw, kMargin * invw + 1e-3f);
-    ilo = max(0, (int)floorf(s.tx - rxc));
-    ihi = min(D - 1, (int)floorf(s.tx + rxc));
+    // both ends clamped like cellFromPoint clamps: a query outside the domain still reaches its border cell
+    ilo = max(0, min(D - 1, (int)floorf(s.tx - rxc)));
+    ihi = max(0, min(D - 1, (int)floorf(s.tx + rxc)));
 }
 
 __device__ __forceinline__ unsigned long long make_key(const float4 c, const QueryGeom &s, int p) {
@@ -294,7 +304,7 @@ __global__ void __launch_bounds__(QB) kn_query_fast_kernel(const __grid_constant
                     const int dj = P.tab.dj[ee], dk = P.tab.dk[ee];
                     const int j = s.cj + dj, k = s.ck + dk;
                     if (j >= 0 && j < D && k >= zb && k < ze) {
-                        const float lbyz2 = row_lower_bound2(s, dj, dk, w);
+                        const float lbyz2 = row_lower_bound2(s, dj, dk, w, P.g);
                         if (lbyz2 <= bound2) {
                             int ilo, ihi;
                             row_x_range(s, bound2, lbyz2, invw, D, ilo, ihi);
@@ -415,7 +425,7 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
                     const int dj = P.tab.dj[ee], dk = P.tab.dk[ee];
                     const int j = s.cj + dj, k = s.ck + dk;
                     if (j >= 0 && j < D && k >= zb && k < ze) {
-                        const float lbyz2 = row_lower_bound2(s, dj, dk, w);
+                        const float lbyz2 = row_lower_bound2(s, dj, dk, w, P.g);
                         if (lbyz2 <= r2) {
                             int ilo, ihi;
                             row_x_range(s, r2, lbyz2, invw, D, ilo, ihi);
@@ -582,7 +592,7 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
         auto scan_row = [&](int dj, int dk) {
             const int j = s.cj + dj, k = s.ck + dk;
             if (j < 0 || j >= D || k < zb || k >= ze) return;
-            const float lbyz2 = row_lower_bound2(s, dj, dk, w);
+            const float lbyz2 = row_lower_bound2(s, dj, dk, w, P.g);
             if (lbyz2 > bound2) { pruned = true; return; }
             int ilo, ihi;
             row_x_range(s, bound2, lbyz2, invw, D, ilo, ihi);
@@ -618,12 +628,14 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
         bool done = !valid;
         while (!done) {
             cnt = 0; kth = ~0ull; bound2 = r2; pruned = false;
-            bool table_exhausted = true;
             for (int e = 0; e < P.tab.n; ++e) {  // rows nearest-first
-                if (P.tab.lb2[e] > bound2) { pruned = true; table_exhausted = false; break; }
+                if (P.tab.lb2[e] > bound2) { pruned = true; break; }
                 scan_row(P.tab.dj[e], P.tab.dk[e]);
             }
-            if (table_exhausted) {  // beyond the table: plain square rings of rows
+            // Beyond the table: plain square rings of rows.  NOT conditional on having walked the whole table:
+            // the table ends with its corner rows (lower bound 4 sqrt(2) cells), which lie farther than the face
+            // rows of the next ring (5 cells), so leaving the table early says nothing about ring 6.
+            {
                 const int rmax = max(max(s.cj, D - 1 - s.cj), max(s.ck - zb, ze - 1 - s.ck));
                 for (int r = kTableRing + 1; r <= rmax; ++r) {
                     const float lb = fmaxf(0.f, (float)(r - 1) * w - kMargin);
