@@ -123,3 +123,18 @@ def test_edge_cases_oracle(oracle):
     rows, d2 = g.knn_exact(4, with_d2=True)
     assert (d2[:, :2] == 0).all() and (d2[:, 2] > 0).all()
     assert (rows != np.arange(150, dtype=np.uint32)[:, None]).all()
+
+
+def test_exact_equals_brute_force_on_random_shapes(oracle):
+    """The grid-accelerated oracle against plain brute force on clouds that break the uniform assumptions:
+    clusters, planes, lines, duplicates, lattices, points outside [0,1000]^3 (clamped into border cells)."""
+    from test_random_differential_gpu import KINDS, make_cloud
+    rng = np.random.default_rng(77)
+    for case in range(70):
+        kind = KINDS[case % len(KINDS)]
+        n = int(rng.choice([1, 2, 5, 60, 400, 2500]))
+        k = int(rng.choice([1, 3, 8, 20, 50]))
+        density = float(rng.choice([0.5, 1.0, 3.1, 10.0]))
+        pts = np.ascontiguousarray(make_cloud(rng, kind, n), np.float32)
+        g = oracle.Grid(pts, density=density)
+        assert np.array_equal(g.knn_exact(k), oracle.brute(g.sorted_xyz, k)), (case, kind, n, k, density)

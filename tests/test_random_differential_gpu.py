@@ -53,3 +53,52 @@ def test_random_clouds_match_the_oracle(kn, oracle, seed):
         want, want_d2 = g.knn_exact(k, with_d2=True)
         assert np.array_equal(rows, want), tag
         assert np.array_equal(d2.view(np.uint32), want_d2.view(np.uint32)), tag
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_random_slabs_external_queries_and_streaming(kn, oracle, seed):
+    """Random z-slab handles (with the halo the driver would give them), external query points and the
+    streamed solve, on random cloud shapes -- against the whole-grid oracle."""
+    import torch
+    from cuda_knearests_b200 import slabs
+    rng = np.random.default_rng(500 + seed)
+    for case in range(8):
+        kind = ["uniform", "clustered", "planar", "out_of_range"][(seed + case) % 4]
+        n = int(rng.choice([3000, 20000, 90000]))
+        k = int(rng.choice([8, 20, 32]))
+        pts = np.ascontiguousarray(make_cloud(rng, kind, n), np.float32)
+        tag = f"seed={seed} case={case} kind={kind} n={n} k={k}"
+        g = oracle.Grid(pts)
+        D = g.dim
+        full = g.knn_exact(k)
+        # streamed solve == plain solve == oracle
+        pinned = torch.empty(full.shape, dtype=torch.int32, pin_memory=True)
+        with kn.KnProblem(pts, k=k) as p:
+            got = p.solve_to_host(pinned.numpy().view(np.uint32), chunks=int(rng.integers(1, 9)))
+            assert np.array_equal(got, full), tag
+            q = np.ascontiguousarray(make_cloud(rng, "out_of_range", 300), np.float32)
+            assert np.array_equal(p.query_points(q), oracle.brute_external(g.sorted_xyz, q, k)), tag
+        # a random slab with generous halo: rows of its owned planes == whole-grid rows (shifted)
+        if D < 8:
+            continue
+        ozb = int(rng.integers(0, D - 2))
+        oze = int(rng.integers(ozb + 1, D + 1))
+        cz = np.clip(np.floor(pts[:, 2] * np.float32(D) / np.float32(1000)).astype(int), 0, D - 1)
+        for halo in (slabs.halo_planes(k), D):  # the driver's halo may be too thin for odd clouds: then it must say so
+            zb, ze = max(0, ozb - halo), min(D, oze + halo)
+            sub = np.ascontiguousarray(pts[(cz >= zb) & (cz < ze)])
+            if len(sub) == 0:
+                break
+            base = int(g.ptrs[zb * D * D])
+            q0, q1 = int(g.ptrs[ozb * D * D]) - base, int(g.ptrs[oze * D * D]) - base
+            with kn.KnProblem(sub, k=k, grid_dim=D, slab=(zb, ze, ozb, oze)) as p:
+                try:
+                    p.solve()
+                except kn.KnError as e:
+                    assert e.code == 5 and halo < D, tag  # KNC_ERR_HALO, only possible with the thin halo
+                    continue
+                rows = p.get_knearests().astype(np.int64)
+            want = full[base + q0: base + q1].astype(np.int64)
+            want = np.where(want == 0xFFFFFFFF, want, want - base)
+            assert np.array_equal(rows, want), tag + f" slab=({zb},{ze},{ozb},{oze})"
+            break
