@@ -158,7 +158,11 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     if (n < 1) return fail(KNC_ERR_INVALID, "knc_prepare: n = %d, need at least 1 point", n);
     const int k = o.k > 0 ? o.k : default_k();
     if (k > KNC_MAX_K) return fail(KNC_ERR_INVALID, "knc_prepare: k = %d exceeds KNC_MAX_K = %d", k, KNC_MAX_K);
-    const float density = o.density > 0.f ? o.density : 3.1f;
+    // points per cell: the caller's choice, else the environment (drop-in callers cannot pass options), else the
+    // reference's 3.1 (knearests.cu:249)
+    float density = 3.1f;
+    if (o.density > 0.f) density = o.density;
+    else if (const char *e = getenv("KN_GRID_DENSITY")) { if (atof(e) > 0.) density = (float)atof(e); }
     const int stride = o.point_stride > 0 ? o.point_stride : 3;
     if (stride != 3 && stride != 4) return fail(KNC_ERR_INVALID, "knc_prepare: point_stride = %d, supported 3 or 4", stride);
     const int D = o.grid_dim > 0 ? o.grid_dim : knc_grid_dim(n, density);
