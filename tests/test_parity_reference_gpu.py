@@ -44,3 +44,24 @@ def test_uniform_against_reference_gpu(kn, oracle, n, K, seed):
     same, ties, bad = oracle.compare_canonical(ia, da, ib, db, ulp_slack=0)
     assert bad == [] and same + ties == n
     assert ties < n // 1000
+
+
+def blue_noise_substitute(n_side: int, seed: int) -> np.ndarray:
+    """Stand-in for the missing 300k_blue_cube.xyz / 900k_blue_cube.xyz: a jittered grid --
+    one point per cell of an n_side^3 lattice, displaced by up to 0.35 of the spacing -- i.e. a cloud without
+    the clumps and voids of a uniform one, scaled into [0,1000]^3 like the reference loader does."""
+    rng = np.random.default_rng(seed)
+    ax = (np.arange(n_side, dtype=np.float64) + 0.5) / n_side
+    g = np.stack(np.meshgrid(ax, ax, ax, indexing="ij"), -1).reshape(-1, 3)
+    g += (rng.random(g.shape) - 0.5) * (0.7 / n_side)
+    return np.ascontiguousarray(rng.permutation(g * 998.0 + 1.0).astype(np.float32))
+
+
+@pytest.mark.parametrize("n_side,seed", [(67, 3), (97, 4)])  # 300 763 and 912 673 points
+def test_blue_noise_substitutes_against_reference_gpu(kn, oracle, n_side, seed):
+    """configs[1]: 300k_blue_cube / 900k_blue_cube are not in the snapshot; labelled substitutes, k = 50."""
+    pts = blue_noise_substitute(n_side, seed)
+    ia, da, ib, db = canonical_pair(oracle, kn, pts, 50)
+    same, ties, bad = oracle.compare_canonical(ia, da, ib, db, ulp_slack=0)
+    assert bad == [] and same + ties == len(pts)
+    assert ties < len(pts) // 1000
