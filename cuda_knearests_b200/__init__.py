@@ -30,6 +30,8 @@ C_ABI_SYMBOLS = [
     "knc_grid_dim", "knc_last_error", "knc_version", "knc_generate_uniform_device", "knc_scan_cells_noalloc",
     "knc_slab_route", "knc_get_knearests_global", "knc_set_index_offset", "knc_get_permutation_global",
     "knc_get_dists", "knc_query_points",
+    "knc_route_begin", "knc_route_scatter", "knc_route_end",
+    "knc_peer_alloc", "knc_peer_open", "knc_peer_close", "knc_peer_free",
 ]
 # the reference's own (C++-mangled) entry points, knearests.h:21-29
 CXX_ABI_SYMBOLS = [
@@ -107,6 +109,14 @@ def lib() -> C.CDLL:
         L.knc_slab_route.argtypes = [vp, C.c_int, C.c_uint, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, vp,
                                      C.c_longlong, C.POINTER(C.c_longlong)]
         L.knc_get_knearests_global.argtypes = [vp, vp, C.c_int, vp, vp]
+        L.knc_route_begin.argtypes = [vp, C.c_int, C.c_uint, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int,
+                                      C.POINTER(vp), C.POINTER(C.c_longlong)]
+        L.knc_route_scatter.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_longlong)]
+        L.knc_route_end.argtypes = [vp]
+        L.knc_peer_alloc.argtypes = [C.c_size_t, C.POINTER(vp), C.c_char_p]
+        L.knc_peer_open.argtypes = [C.c_char_p, C.POINTER(vp)]
+        L.knc_peer_close.argtypes = [vp]
+        L.knc_peer_free.argtypes = [vp]
         L.knc_set_index_offset.argtypes = [vp, C.c_longlong]
         L.knc_get_permutation_global.argtypes = [vp, vp, C.c_int, vp]
         L.knc_last_error.restype = C.c_char_p

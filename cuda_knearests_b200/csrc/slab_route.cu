@@ -13,6 +13,8 @@
 // exactly the single-GPU order (and therefore bit-identical rows).
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
+#include <string.h>
 
 #include "kn_internal.h"
 
@@ -86,11 +88,18 @@ __global__ void __launch_bounds__(1024) kn_route_scan_kernel(int *counts, int nb
     if (tid == 0) totals[blockIdx.x] = s_carry;
 }
 
-// stable scatter: position = base[d] + block offset + rank among the block's earlier points
+// Where the group of each destination goes: a buffer (this GPU's memory, or a PEER GPU's memory mapped into this
+// process -- the stores then travel over NVLink while the kernel runs) and the first record to write there.
+struct RouteDest {
+    float4 *buf[kMaxRanks];
+    long long first[kMaxRanks];
+};
+
+// stable scatter: position = first[d] + block offset + rank among the block's earlier points
 __global__ void __launch_bounds__(kRouteThreads)
 kn_route_scatter_kernel(const float *__restrict__ xyz, int n, unsigned first_id, float Df, int D,
                         const __grid_constant__ RoutePlan pl, int nblocks, const int *__restrict__ offsets,
-                        const long long *__restrict__ base, float4 *__restrict__ out_rec) {
+                        const __grid_constant__ RouteDest dst) {
     __shared__ int s_warp[kMaxRanks][kRouteThreads / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const long long i = (long long)blockIdx.x * kRouteThreads + tid;
@@ -110,8 +119,8 @@ kn_route_scatter_kernel(const float *__restrict__ xyz, int n, unsigned first_id,
         if ((m >> d) & 1u) {
             int before = __popc(b & ((1u << lane) - 1u));
             for (int wq = 0; wq < warp; ++wq) before += s_warp[d][wq];
-            const long long pos = base[d] + offsets[(size_t)d * nblocks + blockIdx.x] + before;
-            out_rec[pos] = make_float4(x, y, z, __uint_as_float(first_id + (unsigned)i));  // one 16-byte store
+            const long long pos = dst.first[d] + offsets[(size_t)d * nblocks + blockIdx.x] + before;
+            dst.buf[d][pos] = make_float4(x, y, z, __uint_as_float(first_id + (unsigned)i));  // one 16-byte store
         }
     }
 }
@@ -153,59 +162,138 @@ extern "C" int knc_get_permutation_global(knc_problem *p, const unsigned int *d_
     return KNC_OK;
 }
 
+// A routing pass in two steps, so that the caller can learn the group sizes (and agree with the other ranks
+// on where each group lands) before any record is written.
+struct knc_route {
+    const float *d_xyz;
+    int n, grid_dim, nblocks;
+    unsigned first_id;
+    RoutePlan pl;
+    int *d_counts;       // [nranks][nblocks] per-block group sizes, then their exclusive scan
+    long long *d_tot;    // [nranks] group totals
+    long long counts[kMaxRanks];
+};
+
+extern "C" int knc_route_begin(const float *d_xyz, int n, unsigned int first_id, int grid_dim, int nranks,
+                               const int *zsplit, int halo, knc_route **out, long long *out_counts) {
+    if (!d_xyz || !zsplit || !out || !out_counts || n < 0 || grid_dim < 1 || halo < 0)
+        return kn_set_error(KNC_ERR_INVALID, "knc_route_begin: bad argument");
+    if (nranks < 1 || nranks > kMaxRanks)
+        return kn_set_error(KNC_ERR_INVALID, "knc_route_begin: nranks = %d, supported 1..%d", nranks, kMaxRanks);
+    *out = nullptr;
+    knc_route *r = (knc_route *)calloc(1, sizeof(knc_route));
+    if (!r) return kn_set_error(KNC_ERR_NOMEM, "knc_route_begin: out of host memory");
+    r->d_xyz = d_xyz; r->n = n; r->grid_dim = grid_dim; r->first_id = first_id;
+    r->pl.nranks = nranks;
+    for (int d = 0; d < nranks; ++d) {
+        if (zsplit[d] > zsplit[d + 1] || zsplit[0] != 0 || zsplit[nranks] != grid_dim) {
+            free(r);
+            return kn_set_error(KNC_ERR_INVALID, "knc_route_begin: zsplit must rise from 0 to grid_dim");
+        }
+        r->pl.lo[d] = zsplit[d] - halo;
+        r->pl.hi[d] = zsplit[d + 1] + halo;
+        if (zsplit[d] == zsplit[d + 1]) r->pl.lo[d] = r->pl.hi[d] = 0;  // an empty slab wants nothing
+        out_counts[d] = 0;
+    }
+    r->nblocks = (n + kRouteThreads - 1) / kRouteThreads;
+    cudaError_t e = cudaSuccess;
+    if (n > 0) {
+        cudaStream_t st = 0;
+        e = cudaMallocAsync((void **)&r->d_counts, sizeof(int) * (size_t)nranks * r->nblocks, st);
+        if (e == cudaSuccess) e = cudaMallocAsync((void **)&r->d_tot, sizeof(long long) * kMaxRanks, st);
+        if (e == cudaSuccess) {
+            kn_route_count_kernel<<<r->nblocks, kRouteThreads, 0, st>>>(d_xyz, n, (float)grid_dim, grid_dim, r->pl, r->nblocks,
+                                                                       r->d_counts);
+            kn_route_scan_kernel<<<nranks, 1024, 0, st>>>(r->d_counts, r->nblocks, r->d_tot);
+            e = cudaMemcpyAsync(r->counts, r->d_tot, sizeof(long long) * nranks, cudaMemcpyDeviceToHost, st);
+        }
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    }
+    if (e != cudaSuccess) {
+        if (r->d_counts) cudaFreeAsync(r->d_counts, 0);
+        if (r->d_tot) cudaFreeAsync(r->d_tot, 0);
+        free(r);
+        return kn_set_error(KNC_ERR_CUDA, "knc_route_begin: %s", cudaGetErrorString(e));
+    }
+    for (int d = 0; d < nranks; ++d) out_counts[d] = r->counts[d];
+    *out = r;
+    return KNC_OK;
+}
+
+extern "C" int knc_route_scatter(knc_route *r, void *const *dest_bufs, const long long *dest_first) {
+    if (!r || !dest_bufs || !dest_first) return kn_set_error(KNC_ERR_INVALID, "knc_route_scatter: NULL argument");
+    if (r->n == 0) return KNC_OK;
+    RouteDest dst;
+    for (int d = 0; d < r->pl.nranks; ++d) {
+        if (r->counts[d] > 0 && (!dest_bufs[d] || ((uintptr_t)dest_bufs[d] & 15u) || dest_first[d] < 0))
+            return kn_set_error(KNC_ERR_INVALID, "knc_route_scatter: destination %d has no usable buffer", d);
+        dst.buf[d] = reinterpret_cast<float4 *>(dest_bufs[d]);
+        dst.first[d] = dest_first[d];
+    }
+    kn_route_scatter_kernel<<<r->nblocks, kRouteThreads, 0, 0>>>(r->d_xyz, r->n, r->first_id, (float)r->grid_dim, r->grid_dim,
+                                                                r->pl, r->nblocks, r->d_counts, dst);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaStreamSynchronize(0);  // the records (also those sent to peers) have landed
+    if (e != cudaSuccess) return kn_set_error(KNC_ERR_CUDA, "knc_route_scatter: %s", cudaGetErrorString(e));
+    return KNC_OK;
+}
+
+extern "C" int knc_route_end(knc_route *r) {
+    if (!r) return KNC_OK;
+    if (r->d_counts) cudaFreeAsync(r->d_counts, 0);
+    if (r->d_tot) cudaFreeAsync(r->d_tot, 0);
+    free(r);
+    return KNC_OK;
+}
+
 extern "C" int knc_slab_route(const float *d_xyz, int n, unsigned int first_id, int grid_dim, int nranks,
                               const int *zsplit, int halo, float *d_out_rec, long long capacity,
                               long long *out_counts) {
-    if (!d_xyz || !zsplit || !d_out_rec || !out_counts || n < 0 || grid_dim < 1 || halo < 0 ||
-        ((uintptr_t)d_out_rec & 15u))
-        return kn_set_error(KNC_ERR_INVALID, "knc_slab_route: bad argument");
-    if (nranks < 1 || nranks > kMaxRanks)
-        return kn_set_error(KNC_ERR_INVALID, "knc_slab_route: nranks = %d, supported 1..%d", nranks, kMaxRanks);
-    RoutePlan pl;
-    pl.nranks = nranks;
-    for (int d = 0; d < nranks; ++d) {
-        if (zsplit[d] > zsplit[d + 1] || zsplit[0] != 0 || zsplit[nranks] != grid_dim)
-            return kn_set_error(KNC_ERR_INVALID, "knc_slab_route: zsplit must rise from 0 to grid_dim");
-        pl.lo[d] = zsplit[d] - halo;
-        pl.hi[d] = zsplit[d + 1] + halo;
-        if (zsplit[d] == zsplit[d + 1]) pl.lo[d] = pl.hi[d] = 0;  // an empty slab wants nothing
-    }
-    for (int d = 0; d < nranks; ++d) out_counts[d] = 0;
-    if (n == 0) return KNC_OK;
-    const int nblocks = (n + kRouteThreads - 1) / kRouteThreads;
-    int *d_counts = nullptr;
-    long long *d_tot = nullptr;  // [nranks] totals, then [nranks] bases
-    long long h[2 * kMaxRanks];
-    cudaStream_t st = 0;
-    cudaError_t e = cudaMallocAsync((void **)&d_counts, sizeof(int) * (size_t)nranks * nblocks, st);
-    if (e == cudaSuccess) e = cudaMallocAsync((void **)&d_tot, sizeof(long long) * 2 * kMaxRanks, st);
-    if (e == cudaSuccess) {
-        kn_route_count_kernel<<<nblocks, kRouteThreads, 0, st>>>(d_xyz, n, (float)grid_dim, grid_dim, pl, nblocks, d_counts);
-        kn_route_scan_kernel<<<nranks, 1024, 0, st>>>(d_counts, nblocks, d_tot);
-        e = cudaMemcpyAsync(h, d_tot, sizeof(long long) * nranks, cudaMemcpyDeviceToHost, st);
-    }
-    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-    int rc = KNC_OK;
-    if (e == cudaSuccess) {
-        long long run = 0;
-        for (int d = 0; d < nranks; ++d) { out_counts[d] = h[d]; h[kMaxRanks + d] = run; run += h[d]; }
-        if (run > capacity) {
-            rc = kn_set_error(KNC_ERR_NOMEM, "knc_slab_route: %lld records to send, output capacity %lld", run, capacity);
-        } else {
-            e = cudaMemcpyAsync(d_tot + kMaxRanks, h + kMaxRanks, sizeof(long long) * nranks, cudaMemcpyHostToDevice, st);
-            if (e == cudaSuccess) {
-                kn_route_scatter_kernel<<<nblocks, kRouteThreads, 0, st>>>(d_xyz, n, first_id, (float)grid_dim, grid_dim, pl,
-                                                                          nblocks, d_counts, d_tot + kMaxRanks,
-                                                                          reinterpret_cast<float4 *>(d_out_rec));
-                e = cudaGetLastError();
-            }
-            if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-        }
-    }
-    if (d_counts) cudaFreeAsync(d_counts, st);
-    if (d_tot) cudaFreeAsync(d_tot, st);
-    if (e != cudaSuccess) return kn_set_error(KNC_ERR_CUDA, "knc_slab_route: %s", cudaGetErrorString(e));
+    if (!d_out_rec || ((uintptr_t)d_out_rec & 15u)) return kn_set_error(KNC_ERR_INVALID, "knc_slab_route: bad output buffer");
+    knc_route *r = nullptr;
+    int rc = knc_route_begin(d_xyz, n, first_id, grid_dim, nranks, zsplit, halo, &r, out_counts);
+    if (rc != KNC_OK) return rc;
+    void *bufs[kMaxRanks];
+    long long first[kMaxRanks], run = 0;
+    for (int d = 0; d < nranks; ++d) { bufs[d] = d_out_rec; first[d] = run; run += out_counts[d]; }
+    if (run > capacity)
+        rc = kn_set_error(KNC_ERR_NOMEM, "knc_slab_route: %lld records to send, output capacity %lld", run, capacity);
+    else
+        rc = knc_route_scatter(r, bufs, first);
+    knc_route_end(r);
     return rc;
+}
+
+// ---- peer buffers: device memory that other ranks (processes) of the node can write into -------------------------
+extern "C" int knc_peer_alloc(size_t bytes, void **d_ptr, unsigned char *handle64) {
+    if (!d_ptr || !handle64 || bytes == 0) return kn_set_error(KNC_ERR_INVALID, "knc_peer_alloc: bad argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    cudaError_t e = cudaMalloc(d_ptr, bytes);  // plain cudaMalloc: pool memory cannot be exported
+    cudaIpcMemHandle_t h;
+    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, *d_ptr);
+    if (e != cudaSuccess) return kn_set_error(e == cudaErrorMemoryAllocation ? KNC_ERR_NOMEM : KNC_ERR_CUDA, "knc_peer_alloc: %s",
+                                              cudaGetErrorString(e));
+    memcpy(handle64, &h, 64);
+    return KNC_OK;
+}
+
+extern "C" int knc_peer_open(const unsigned char *handle64, void **d_ptr) {
+    if (!handle64 || !d_ptr) return kn_set_error(KNC_ERR_INVALID, "knc_peer_open: NULL argument");
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    cudaError_t e = cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) return kn_set_error(KNC_ERR_CUDA, "knc_peer_open: %s", cudaGetErrorString(e));
+    return KNC_OK;
+}
+
+extern "C" int knc_peer_close(void *d_ptr) {
+    if (d_ptr && cudaIpcCloseMemHandle(d_ptr) != cudaSuccess) return kn_set_error(KNC_ERR_CUDA, "knc_peer_close failed");
+    return KNC_OK;
+}
+
+extern "C" int knc_peer_free(void *d_ptr) {
+    if (d_ptr && cudaFree(d_ptr) != cudaSuccess) return kn_set_error(KNC_ERR_CUDA, "knc_peer_free failed");
+    return KNC_OK;
 }
 
 extern "C" int knc_get_knearests_global(knc_problem *p, const unsigned int *d_ids, int id_stride,

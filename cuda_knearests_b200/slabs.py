@@ -20,6 +20,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import os
 import time
 
 import numpy as np
@@ -92,6 +93,75 @@ def record_ids(rec):
     return rec.view(torch.int32)[:, 3]
 
 
+class PeerExchange:
+    """Receive buffers of all ranks of the node, mapped into every process (CUDA IPC), so that the routing kernel
+    writes each group straight into its destination GPU's memory over NVLink: routing + exchange in ONE kernel, no
+    send buffer and no NCCL all-to-all (the only collectives left are an all-gather of W group sizes and a barrier).
+    Created once per process group and reused by every step."""
+
+    def __init__(self, capacity_records: int, group=None):
+        import torch
+        import torch.distributed as dist
+        import cuda_knearests_b200 as K
+        self.K, self.group = K, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.capacity = int(capacity_records)
+        mine = C.c_void_p()
+        handle = C.create_string_buffer(64)
+        K._check(K.lib().knc_peer_alloc(self.capacity * 16, C.byref(mine), handle))
+        self.local = mine.value
+        handles = [None] * self.world
+        dist.all_gather_object(handles, handle.raw, group=group)
+        self.bufs = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                self.bufs.append(self.local)
+            else:
+                p = C.c_void_p()
+                K._check(K.lib().knc_peer_open(h, C.byref(p)))
+                self.bufs.append(p.value)
+        dist.barrier(group=group)
+
+    def route(self, local_xyz, first_id: int, D: int, zsplit, halo: int):
+        """Route this rank's chunk into everybody's receive buffer.  Returns (records_received, torch view [m,4]
+        of the local receive buffer, records_sent) or raises if a receive buffer would overflow."""
+        import torch
+        import torch.distributed as dist
+        K, L = self.K, self.K.lib()
+        W = self.world
+        dev = local_xyz.device
+        zs = (C.c_int * (W + 1))(*zsplit)
+        counts = (C.c_longlong * W)()
+        h = C.c_void_p()
+        K._check(L.knc_route_begin(C.c_void_p(local_xyz.data_ptr()), local_xyz.shape[0], first_id, D, W, zs, halo,
+                                   C.byref(h), counts))
+        try:
+            allc = torch.empty((W, W), dtype=torch.int64, device=dev)  # allc[s][d] = records rank s sends to rank d
+            dist.all_gather_into_tensor(allc, torch.tensor(list(counts), dtype=torch.int64, device=dev), group=self.group)
+            allc = allc.tolist()
+            incoming = [sum(allc[s][d] for s in range(W)) for d in range(W)]
+            if max(incoming) > self.capacity:
+                raise K.KnError(3, f"peer receive buffer holds {self.capacity} records, {max(incoming)} are on their way")
+            first = (C.c_longlong * W)(*[sum(allc[s][d] for s in range(self.rank)) for d in range(W)])
+            bufs = (C.c_void_p * W)(*self.bufs)
+            K._check(L.knc_route_scatter(h, bufs, first))
+        finally:
+            L.knc_route_end(h)
+        dist.barrier(group=self.group)  # every rank's stores have landed (each scatter call returned after its sync)
+        m = incoming[self.rank]
+        view = torch.as_tensor(_DevView(self.local, (m, 4), "<f4"), device=dev) if m else torch.empty((0, 4), device=dev)
+        return view, int(sum(counts))
+
+    def close(self):
+        L = self.K.lib()
+        for r, p in enumerate(self.bufs):
+            if r != self.rank and p:
+                L.knc_peer_close(C.c_void_p(p))
+        if self.local:
+            L.knc_peer_free(C.c_void_p(self.local))
+        self.bufs, self.local = [], None
+
+
 class SlabRows:
     """Result of one rank, in the single-GPU contract made global:
       rows        view of the handle's d_knearests: [query_count, k] GLOBAL sorted positions (torch, device)
@@ -115,12 +185,14 @@ class _DevView:
 
 
 def solve_distributed(local_xyz, first_id: int, n_total: int, k: int, group=None, halo: int | None = None,
-                      density: float = 3.1, phases: dict | None = None, host_rows=None) -> SlabRows:
+                      density: float = 3.1, phases: dict | None = None, host_rows=None,
+                      peers: PeerExchange | None = None) -> SlabRows:
     """One pass of the multi-GPU hot path on this rank's chunk (CUDA tensor [n_local, 3]).
     `phases` (optional dict) receives wall-clock milliseconds per phase, with a device sync after each
     (diagnostic runs only: the syncs are not free).  `host_rows` (optional page-locked uint32 numpy array with
     room for this rank's rows) makes the solve stream its rows to the host while computing
-    (knc_solve_to_host)."""
+    (knc_solve_to_host).  `peers` (a PeerExchange) replaces route + NCCL all-to-all by the fused
+    route-into-peer-memory kernel."""
     import torch
     import torch.distributed as dist
     import cuda_knearests_b200 as K
@@ -141,13 +213,18 @@ def solve_distributed(local_xyz, first_id: int, n_total: int, k: int, group=None
     while True:
         info["attempts"] += 1
         info["halo"] = halo
-        send_rec, counts = route_device(local_xyz, first_id, D, zsplit, halo)
-        mark("route")
-        recv_xyz, recv_counts = exchange(send_rec, counts, group)  # [m,4] records: x, y, z, bits(global id)
-        mark("exchange")
-        del send_rec
+        if peers is not None:
+            recv_xyz, sent = peers.route(local_xyz, first_id, D, zsplit, halo)  # [m,4] records: x, y, z, bits(global id)
+            mark("route_into_peers")
+        else:
+            send_rec, counts = route_device(local_xyz, first_id, D, zsplit, halo)
+            mark("route")
+            recv_xyz, recv_counts = exchange(send_rec, counts, group)
+            mark("exchange")
+            sent = int(sum(counts))
+            del send_rec
         zb, ze, ozb, oze = held_planes(zsplit, rank, halo, D)
-        info.update(points_held=int(recv_xyz.shape[0]), sent=int(sum(counts)), planes=(zb, ze, ozb, oze))
+        info.update(points_held=int(recv_xyz.shape[0]), sent=sent, planes=(zb, ze, ozb, oze))
         p = None
         mine = [0, 0]
         if oze > ozb and recv_xyz.shape[0] > 0:
@@ -204,9 +281,11 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
     n, k = args.n, args.k
     lo, hi = (rank * n) // world, ((rank + 1) * n) // world
     pts = K.generate_uniform_device(hi - lo, seed=SEED, first=lo, device=dev)
+    # receive buffers of all ranks mapped into every process: 1.25x the even share + the halo, generous for uniform clouds
+    peers = None if os.environ.get("KN_EXCHANGE", "p2p") == "nccl" else PeerExchange(int(1.35 * n / world) + (1 << 20))
 
     def step():
-        r = solve_distributed(pts, lo, n, k, density=args.density or 3.1)
+        r = solve_distributed(pts, lo, n, k, density=args.density or 3.1, peers=peers)
         info = r.info
         r.free()
         return info
@@ -231,7 +310,7 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
         phase_ms.clear()
         torch.cuda.synchronize()
         tt = time.perf_counter()
-        rr = solve_distributed(pts, lo, n, k, density=args.density or 3.1, phases=phase_ms)
+        rr = solve_distributed(pts, lo, n, k, density=args.density or 3.1, phases=phase_ms, peers=peers)
         torch.cuda.synchronize()
         t1 = time.perf_counter()
         rr.free()
@@ -255,7 +334,7 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
 
         def step_e2e():
             d_in = host_in.to(dev, non_blocking=True)
-            r = solve_distributed(d_in, lo, n, k, density=args.density or 3.1, host_rows=host_rows_np)
+            r = solve_distributed(d_in, lo, n, k, density=args.density or 3.1, host_rows=host_rows_np, peers=peers)
             nq = r.rows.shape[0]
             host_qid[:nq].copy_(r.permutation, non_blocking=True)
             torch.cuda.synchronize()
@@ -287,7 +366,9 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
         cfg.update(parallelism=f"z-slabs x{world}", halo_planes=infos[-1]["halo"], grid_dim=infos[-1]["grid_dim"],
                    points_held_per_rank=[int(s[3].item()) for s in allstats],
                    records_sent_per_rank=[int(s[4].item()) for s in allstats],
-                   exchange="NCCL all_to_all_single of (xyz, id) records, inside the timed step")
+                   exchange=("routing kernel stores every group straight into the destination GPU's receive buffer over "
+                             "NVLink (CUDA IPC peer memory) + all-gather of the group sizes + barrier, inside the timed step"
+                             if peers is not None else "NCCL all_to_all_single of 16-byte records, inside the timed step"))
         line = {"metric": METRIC, "value": n / (wall / args.steps), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
@@ -304,4 +385,6 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
                 "phase_ms_rank0_instrumented": {kk: round(v, 3) for kk, v in phase_ms.items()}}
         print(json.dumps(line), flush=True)
     dist.barrier()
+    if peers is not None:
+        peers.close()
     dist.destroy_process_group()

@@ -183,6 +183,27 @@ int knc_generate_uniform_device(float *d_xyz, long long first, long long count, 
 int knc_slab_route(const float *d_xyz, int n, unsigned int first_id, int grid_dim, int nranks, const int *zsplit,
                    int halo, float *d_out_rec, long long capacity, long long *out_counts);
 
+/* The same routing in two steps, for an exchange WITHOUT a staging copy: knc_route_begin counts the groups
+ * (out_counts, HOST) and keeps its scratch; the ranks agree where each group lands (an all-gather of the
+ * counts); knc_route_scatter then writes group d straight to dest_bufs[d] + dest_first[d] records -- a buffer in
+ * this GPU's memory or in a PEER GPU's memory mapped into this process (knc_peer_open), in which case the
+ * 16-byte stores travel over NVLink while the kernel runs: routing and exchange are one kernel, no NCCL
+ * all-to-all, no send buffer.  dest_bufs / dest_first: HOST arrays of nranks entries.  Blocking; after it returns
+ * and the ranks have met at a barrier, every receive buffer is complete.  knc_route_end releases the scratch. */
+typedef struct knc_route knc_route;
+int knc_route_begin(const float *d_xyz, int n, unsigned int first_id, int grid_dim, int nranks, const int *zsplit,
+                    int halo, knc_route **out, long long *out_counts);
+int knc_route_scatter(knc_route *r, void *const *dest_bufs, const long long *dest_first);
+int knc_route_end(knc_route *r);
+
+/* Receive buffers other processes of the node can write into (CUDA IPC): knc_peer_alloc = cudaMalloc + a 64-byte
+ * handle to hand to the other ranks; knc_peer_open maps another rank's buffer into this process (peer access is
+ * enabled on first use); knc_peer_close / knc_peer_free undo them. */
+int knc_peer_alloc(size_t bytes, void **d_ptr, unsigned char *handle64);
+int knc_peer_open(const unsigned char *handle64, void **d_ptr);
+int knc_peer_close(void *d_ptr);
+int knc_peer_free(void *d_ptr);
+
 /* Slab handles keep the single-GPU contract globally.  Because every rank holds its planes in global
  * order, local sorted position + a constant = GLOBAL sorted position (the constant: points in all lower
  * planes minus this handle's query_begin; the caller gets it from an all-gather of the ranks' query
