@@ -21,6 +21,7 @@ from __future__ import annotations
 import ctypes as C
 import math
 import os
+import sys
 import time
 
 import numpy as np
@@ -100,27 +101,43 @@ class PeerExchange:
     Created once per process group and reused by every step."""
 
     def __init__(self, capacity_records: int, group=None):
+        """Collective.  Raises KnError on EVERY rank if any rank could not allocate, export or map a buffer
+        (the ranks vote), so that callers can switch to the staged exchange together."""
         import torch
         import torch.distributed as dist
         import cuda_knearests_b200 as K
         self.K, self.group = K, group
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.capacity = int(capacity_records)
+        self.bufs, self.local = [], None
+        L = K.lib()
         mine = C.c_void_p()
         handle = C.create_string_buffer(64)
-        K._check(K.lib().knc_peer_alloc(self.capacity * 16, C.byref(mine), handle))
-        self.local = mine.value
+        err = None
+        if L.knc_peer_alloc(self.capacity * 16, C.byref(mine), handle) == 0:
+            self.local = mine.value
+        else:
+            err = L.knc_last_error().decode()
         handles = [None] * self.world
-        dist.all_gather_object(handles, handle.raw, group=group)
-        self.bufs = []
-        for r, h in enumerate(handles):
-            if r == self.rank:
-                self.bufs.append(self.local)
-            else:
+        dist.all_gather_object(handles, handle.raw if self.local else None, group=group)
+        if all(h is not None for h in handles):
+            for r, h in enumerate(handles):
+                if r == self.rank:
+                    self.bufs.append(self.local)
+                    continue
                 p = C.c_void_p()
-                K._check(K.lib().knc_peer_open(h, C.byref(p)))
+                if L.knc_peer_open(h, C.byref(p)) != 0:
+                    err = err or L.knc_last_error().decode()
+                    break
                 self.bufs.append(p.value)
-        dist.barrier(group=group)
+        else:
+            err = err or "another rank could not allocate its receive buffer"
+        dev = torch.device("cuda", torch.cuda.current_device())
+        flag = torch.tensor([0 if err else 1], dtype=torch.int32, device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        if int(flag.item()) == 0:
+            self.close()
+            raise K.KnError(2, f"peer exchange unavailable: {err or 'another rank failed'}")
 
     def route(self, local_xyz, first_id: int, D: int, zsplit, halo: int):
         """Route this rank's chunk into everybody's receive buffer.  Returns (records_received, torch view [m,4]
@@ -282,7 +299,13 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
     lo, hi = (rank * n) // world, ((rank + 1) * n) // world
     pts = K.generate_uniform_device(hi - lo, seed=SEED, first=lo, device=dev)
     # receive buffers of all ranks mapped into every process: 1.25x the even share + the halo, generous for uniform clouds
-    peers = None if os.environ.get("KN_EXCHANGE", "p2p") == "nccl" else PeerExchange(int(1.35 * n / world) + (1 << 20))
+    peers = None
+    if os.environ.get("KN_EXCHANGE", "p2p") != "nccl":
+        try:
+            peers = PeerExchange(int(1.35 * n / world) + (1 << 20))
+        except K.KnError as e:  # raised on every rank together: all switch to the staged NCCL exchange
+            if rank == 0:
+                print(f"bench: {e}; using the staged NCCL exchange", file=sys.stderr)
 
     def step():
         r = solve_distributed(pts, lo, n, k, density=args.density or 3.1, peers=peers)
