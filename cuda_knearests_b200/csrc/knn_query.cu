@@ -384,7 +384,7 @@ __global__ void __launch_bounds__(QB) kn_query_fast_kernel(const __grid_constant
 // k <= count <= capacity  =>  the row is exact (the whole sphere was searched and holds >= k points);
 // anything else goes to the retry list of the general kernel.
 // NET keys are sorted per round, CAP candidates can be buffered per lane (32-bit positions):
-//   k <= 20 : NET 32, CAP 48      k <= 50 : NET 64, CAP 96
+//   k <= 20 : NET 32, CAP 52      k <= 50 : NET 64, CAP 96
 #ifndef KN_SEL_CHUNK
 #define KN_SEL_CHUNK 4
 #endif
@@ -692,7 +692,7 @@ cudaError_t launch(const QueryParams &P, bool fast, cudaStream_t st) {
     constexpr bool kHasSelect = K_T == 8 || K_T == 20 || K_T == 32 || K_T == 50;
     if (fast && kHasSelect && P.use_select) {
         if constexpr (kHasSelect) {
-            constexpr int NET = K_T <= 20 ? 32 : 64, CAP = K_T <= 20 ? 48 : 96;
+            constexpr int NET = K_T <= 20 ? 32 : 64, CAP = K_T <= 20 ? 52 : 96;  // 52: the most that still lets 6 blocks share an SM
             const size_t smem = (sizeof(unsigned) * CAP + sizeof(int2) * kSpanSlots) * QB;
             e = cudaFuncSetAttribute(kn_query_select_kernel<K_T, QB, NET, CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)smem);
