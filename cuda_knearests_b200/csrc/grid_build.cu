@@ -287,40 +287,91 @@ kn_order_big_kernel(const int *big_count, const int *__restrict__ big_list, cons
 // tens of MB -- L2-resident on B200 (126 MB) -- and the build drops to ~1/3 (profiles/r1_notes.md).
 // Stable (input order kept inside a band), so "ascending record position" inside a cell is still
 // "ascending original index" and the layout stays the deterministic stable counting sort.
-constexpr int kBins = 64;
+constexpr int kBins = 64;       // 6 bits: the warp-level grouping below votes once per bit
 constexpr int kBinThreads = 1024;
+constexpr int kBinItems = 4;    // points per thread, all loaded before the first barrier (memory-level parallelism)
+constexpr int kBinTile = kBinThreads * kBinItems;
+constexpr int kBinGroups = kBinItems * (kBinThreads / 32);  // warp-sized runs of consecutive points in a tile
 
-__device__ __forceinline__ int bin_of(const float *rec, const GridGeom &g, int planes_per_bin) {
-    return (axis_cell(__ldg(rec + 2), g.Df, g.zb, g.ze - 1) - g.zb) / planes_per_bin;
+__device__ __forceinline__ int bin_of_z(float z, const GridGeom &g, int planes_per_bin) {
+    return (axis_cell(z, g.Df, g.zb, g.ze - 1) - g.zb) / planes_per_bin;
 }
 
-// rank of this thread among the block's earlier threads of the same bin, and the block's bin counts
-__device__ __forceinline__ int bin_rank_in_block(int bin, bool valid, int (*s_cnt)[kBins]) {
+// lanes of the warp holding the same band (6 votes; only meaningful on valid lanes)
+__device__ __forceinline__ unsigned same_bin_lanes(int bin, bool valid) {
+    unsigned peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+    for (int b = 0; b < 6; ++b) {
+        const bool bit = (bin >> b) & 1;
+        const unsigned m = __ballot_sync(0xffffffffu, bit);
+        peers &= bit ? m : ~m;
+    }
+    return peers;
+}
+
+// A tile is kBinTile consecutive points; item r of thread t is point  tile*kBinTile + r*kBinThreads + t,  so the
+// warp-sized run  v = r*32 + warp  comes before run v+1 in input order.  On return before[r] is the number of
+// tile points of the same band that precede item r, and s_cnt[kBinGroups][b] the tile's count of band b.
+__device__ __forceinline__ void bin_ranks_in_tile(const int (&bin)[kBinItems], const bool (&valid)[kBinItems],
+                                                  int (&before)[kBinItems], int (*s_cnt)[kBins]) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < (kBinThreads / 32) * kBins; i += kBinThreads) (&s_cnt[0][0])[i] = 0;
+    for (int i = tid; i < (kBinGroups + 1) * kBins; i += kBinThreads) (&s_cnt[0][0])[i] = 0;
     __syncthreads();
-    const unsigned peers = __match_any_sync(0xffffffffu, valid ? bin : -1 - lane);
-    if (valid && lane == __ffs(peers) - 1) s_cnt[warp][bin] = __popc(peers);
+#pragma unroll
+    for (int r = 0; r < kBinItems; ++r) {
+        const unsigned peers = same_bin_lanes(bin[r], valid[r]);
+        if (valid[r] && lane == __ffs(peers) - 1) s_cnt[r * 32 + warp][bin[r]] = __popc(peers);
+        before[r] = __popc(peers & ((1u << lane) - 1u));
+    }
     __syncthreads();
-    int before = __popc(peers & ((1u << lane) - 1u));
-    if (valid)
-        for (int wq = 0; wq < warp; ++wq) before += s_cnt[wq][bin];
-    return before;
+    // exclusive prefix over the runs, per band: thread (band, chunk of 8 runs) scans its chunk, then adds the chunks below
+    constexpr int kChunk = 8, kChunks = kBinGroups / kChunk;
+    static_assert(kChunks * kBins == kBinThreads, "one thread per (band, chunk)");
+    __shared__ int s_chunk[kChunks][kBins];
+    const int band = tid & (kBins - 1), chunk = tid / kBins;
+    int run = 0;
+#pragma unroll
+    for (int j = 0; j < kChunk; ++j) {
+        const int c = s_cnt[chunk * kChunk + j][band];
+        s_cnt[chunk * kChunk + j][band] = run;
+        run += c;
+    }
+    s_chunk[chunk][band] = run;
+    __syncthreads();
+    int below = 0;
+    for (int q = 0; q < chunk; ++q) below += s_chunk[q][band];
+#pragma unroll
+    for (int j = 0; j < kChunk; ++j) s_cnt[chunk * kChunk + j][band] += below;
+    if (chunk == kChunks - 1) s_cnt[kBinGroups][band] = below + run;
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < kBinItems; ++r)
+        if (valid[r]) before[r] += s_cnt[r * 32 + warp][bin[r]];
 }
 
 __global__ void __launch_bounds__(kBinThreads)
 kn_bin_count_kernel(const float *__restrict__ xyz, int stride, int n, GridGeom g, int planes_per_bin, int nblocks,
                     int *__restrict__ blockcounts) {
-    __shared__ int s_cnt[kBinThreads / 32][kBins];
-    const long long i = (long long)blockIdx.x * kBinThreads + threadIdx.x;
-    const bool valid = i < n;
-    const int bin = valid ? bin_of(xyz + i * stride, g, planes_per_bin) : 0;
-    bin_rank_in_block(bin, valid, s_cnt);
-    if (threadIdx.x < kBins) {
-        int c = 0;
-        for (int wq = 0; wq < kBinThreads / 32; ++wq) c += s_cnt[wq][threadIdx.x];
-        blockcounts[(size_t)threadIdx.x * nblocks + blockIdx.x] = c;
+    __shared__ int s_hist[kBins];
+    if (threadIdx.x < kBins) s_hist[threadIdx.x] = 0;
+    const long long base = (long long)blockIdx.x * kBinTile + threadIdx.x;
+    float z[kBinItems];
+#pragma unroll
+    for (int r = 0; r < kBinItems; ++r) {
+        const long long i = base + (long long)r * kBinThreads;
+        z[r] = i < n ? __ldg(xyz + i * stride + 2) : 0.f;
     }
+    __syncthreads();
+    const int lane = threadIdx.x & 31;
+#pragma unroll
+    for (int r = 0; r < kBinItems; ++r) {
+        const bool valid = base + (long long)r * kBinThreads < n;
+        const int bin = bin_of_z(z[r], g, planes_per_bin);
+        const unsigned peers = same_bin_lanes(bin, valid);
+        if (valid && lane == __ffs(peers) - 1) atomicAdd(&s_hist[bin], __popc(peers));
+    }
+    __syncthreads();
+    if (threadIdx.x < kBins) blockcounts[(size_t)threadIdx.x * nblocks + blockIdx.x] = s_hist[threadIdx.x];
 }
 
 // one block per bin: exclusive scan of its row of per-block counts (in place), row total to totals[bin]
@@ -354,22 +405,32 @@ __global__ void __launch_bounds__(1024) kn_bin_scan_kernel(int *blockcounts, int
 __global__ void __launch_bounds__(kBinThreads)
 kn_bin_scatter_kernel(const float *__restrict__ xyz, int stride, int n, GridGeom g, int planes_per_bin, int nblocks,
                       const int *__restrict__ offsets, const int *__restrict__ totals, float4 *__restrict__ recs) {
-    __shared__ int s_cnt[kBinThreads / 32][kBins];
+    __shared__ int s_cnt[kBinGroups + 1][kBins];
     __shared__ int s_base[kBins];
-    const long long i = (long long)blockIdx.x * kBinThreads + threadIdx.x;
-    const bool valid = i < n;
-    const float *rec = xyz + (valid ? i : 0) * stride;
-    const int bin = valid ? bin_of(rec, g, planes_per_bin) : 0;
-    if (threadIdx.x < kBins) {  // first record of each band: the totals of the lower bands
+    const long long base = (long long)blockIdx.x * kBinTile + threadIdx.x;
+    float x[kBinItems], y[kBinItems], z[kBinItems];
+    bool valid[kBinItems];
+    int bin[kBinItems], before[kBinItems];
+#pragma unroll
+    for (int r = 0; r < kBinItems; ++r) {
+        const long long i = base + (long long)r * kBinThreads;
+        valid[r] = i < n;
+        const float *rec = xyz + (valid[r] ? i : 0) * stride;
+        x[r] = __ldg(rec); y[r] = __ldg(rec + 1); z[r] = __ldg(rec + 2);
+    }
+    if (threadIdx.x < kBins) {  // first record of each band (the totals of the lower bands) + this tile's start inside it
         int b = 0;
         for (int q = 0; q < (int)threadIdx.x; ++q) b += __ldg(totals + q);
-        s_base[threadIdx.x] = b;
+        s_base[threadIdx.x] = b + __ldg(offsets + (size_t)threadIdx.x * nblocks + blockIdx.x);
     }
-    const int before = bin_rank_in_block(bin, valid, s_cnt);  // contains the barriers that publish s_base
-    if (valid) {
-        const int pos = s_base[bin] + __ldg(offsets + (size_t)bin * nblocks + blockIdx.x) + before;
-        recs[pos] = make_float4(__ldg(rec), __ldg(rec + 1), __ldg(rec + 2), __uint_as_float((unsigned)i));
-    }
+#pragma unroll
+    for (int r = 0; r < kBinItems; ++r) bin[r] = bin_of_z(z[r], g, planes_per_bin);
+    bin_ranks_in_tile(bin, valid, before, s_cnt);  // contains the barriers that publish s_base
+#pragma unroll
+    for (int r = 0; r < kBinItems; ++r)
+        if (valid[r])
+            recs[s_base[bin[r]] + before[r]] =
+                make_float4(x[r], y[r], z[r], __uint_as_float((unsigned)(base + (long long)r * kBinThreads)));
 }
 
 // --------------------------------------------------------------------------------------- gather
@@ -444,7 +505,7 @@ cudaError_t kn_launch_build(const float *d_in_xyz, int stride, int n, const Grid
     if (s.d_bin_recs) {  // large cloud: stable split into z-bands first (see "bins" above)
         const int planes = g.ze - g.zb;
         const int planes_per_bin = (planes + kBins - 1) / kBins;
-        const int nblocks = (int)blocks_for(n, kBinThreads);
+        const int nblocks = (int)blocks_for(n, kBinTile);
         kn_bin_count_kernel<<<nblocks, kBinThreads, 0, st>>>(d_in_xyz, stride, n, g, planes_per_bin, nblocks, s.d_bin_counts);
         kn_bin_scan_kernel<<<kBins, 1024, 0, st>>>(s.d_bin_counts, nblocks, s.d_bin_counts + (size_t)kBins * nblocks);
         kn_bin_scatter_kernel<<<nblocks, kBinThreads, 0, st>>>(d_in_xyz, stride, n, g, planes_per_bin, nblocks, s.d_bin_counts,
@@ -468,7 +529,7 @@ cudaError_t kn_launch_build(const float *d_in_xyz, int stride, int n, const Grid
     return cudaGetLastError();
 }
 
-size_t kn_bin_counts_ints(int n) { return (size_t)kBins * blocks_for(n, kBinThreads) + kBins; }
+size_t kn_bin_counts_ints(int n) { return (size_t)kBins * blocks_for(n, kBinTile) + kBins; }
 
 cudaError_t kn_launch_generate(float *d_xyz, long long first, long long count, uint64_t seed, cudaStream_t st) {
     const long long count3 = count * 3;
