@@ -384,11 +384,25 @@ __global__ void __launch_bounds__(QB) kn_query_fast_kernel(const __grid_constant
 // k <= count <= capacity  =>  the row is exact (the whole sphere was searched and holds >= k points);
 // anything else goes to the retry list of the general kernel.
 // NET keys are sorted per round, CAP candidates can be buffered per lane (32-bit positions):
-//   k <= 20 : NET 32, CAP 52      k <= 50 : NET 64, CAP 96
+//   k <= 20 : NET 32, CAP 56      k <= 50 : NET 64, CAP 100   (the last kSelChunk slots are overrun room,
+//   and the query itself takes one)
 #ifndef KN_SEL_CHUNK
 #define KN_SEL_CHUNK 4
 #endif
 constexpr int kSelChunk = KN_SEL_CHUNK;  // candidates a lane takes per lock-step iteration
+
+// c[U] = src[U] for every U < kSelChunk with at + U < stop, as predicated 16-byte loads at immediate offsets
+// from one base address; records that are not loaded keep their old register contents.
+template <int U>
+__device__ __forceinline__ void load_records_if(float4 (&c)[kSelChunk], int at, int stop, const float4 *src) {
+    if constexpr (U < kSelChunk) {
+        asm("{\n\t.reg .pred p;\n\tsetp.lt.s32 p, %4, %5;\n\t"
+            "@p ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%6+%7];\n\t}"
+            : "+f"(c[U].x), "+f"(c[U].y), "+f"(c[U].z), "+f"(c[U].w)
+            : "r"(at + U), "r"(stop), "l"(src), "n"(16 * U));
+        load_records_if<U + 1>(c, at, stop, src);
+    }
+}
 
 template <int K_T, int QB, int NET, int CAP>
 __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_constant__ QueryParams P) {
@@ -408,7 +422,14 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
     const int q = P.query_begin + (int)min(row0 + tid, (long long)P.query_count - 1);
     const QueryGeom s = query_geom(__ldg(P.pts + q), P.g);
     const float r2 = P.radius0_sq;
-    int cnt = 0;            // candidates seen inside the sphere (may exceed the capacity: then the query is retried)
+    // Append pointer (shared-memory address of the lane's next free buffer slot).  It is clamped once per
+    // chunk, so a chunk may run kSelChunk slots past `wlim`: reaching wlim at all counts as an overflow.
+    const unsigned wp0 = (unsigned)__cvta_generic_to_shared(BUF);
+    const unsigned wlim = wp0 + (unsigned)(kSelectCap - kSelChunk) * QB * 4u;
+    unsigned wp = wp0;
+    float4 ca[kSelChunk], cb[kSelChunk];  // the two record buffers of the pipelined scan (see below)
+#pragma unroll
+    for (int u = 0; u < kSelChunk; ++u) ca[u] = cb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
 
     // ---- search the sphere: rows in batches, spans first, then a lock-step stream over them -----------------
     for (int e0 = 0, e1 = min(kFirstBatch, P.tab.n); e0 < P.tab.n && P.tab.lb2[e0] <= r2;
@@ -450,22 +471,27 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
         // buffers used in turn; the scan is bound by load latency at this occupancy).
         int sp = 0, p = 0, end = 0;
         if (nsp > 0) { const int2 t = SP[0]; p = t.x; end = t.y; sp = 1; }
+        // Loads and the append are predicated instructions written out by hand.  The compiler's version
+        // zeroed the four destination registers before every predicated load and spent seven instructions
+        // on "if (pass) BUF[min(cnt, cap)] = i; cnt += pass" (select 0/1, add, clamp, multiply-add, store):
+        // 23 instructions per candidate in all, in a kernel that is bound by instruction issue.  A record that
+        // is not loaded keeps stale values, which is harmless: the append tests the same index bound again.
         auto fetch = [&](float4(&c)[kSelChunk], int at, int stop) {
-#pragma unroll
-            for (int u = 0; u < kSelChunk; ++u) {
-                c[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (at + u < stop) c[u] = __ldg(P.pts + at + u);
-            }
+            load_records_if<0>(c, at, stop, P.pts + at);
         };
-        auto evaluate = [&](float4(&c)[kSelChunk], int at, int stop) {  // branch-free: only the append is predicated
+        // The query itself is appended too (it is inside every sphere) and dropped when the keys are rebuilt:
+        // one test per buffered candidate instead of one per scanned candidate (self excluded, knearests.cu:123).
+        auto evaluate = [&](float4(&c)[kSelChunk], int at, int stop) {
 #pragma unroll
             for (int u = 0; u < kSelChunk; ++u) {
                 const float dx = c[u].x - s.px, dy = c[u].y - s.py, dz = c[u].z - s.pz;
                 const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
-                const bool pass = (at + u < stop) & (d2 <= r2) & (at + u != q);  // self excluded, knearests.cu:123
-                if (pass) BUF[min(cnt, kSelectCap - 1) * QB] = (unsigned)(at + u);  // beyond the capacity: retried anyway
-                cnt += pass ? 1 : 0;
+                asm volatile("{\n\t.reg .pred p;\n\tsetp.le.f32 p, %1, %2;\n\tsetp.lt.and.s32 p, %3, %4, p;\n\t"
+                             "@p st.shared.u32 [%0], %3;\n\t@p add.u32 %0, %0, %5;\n\t}"
+                             : "+r"(wp)
+                             : "f"(d2), "f"(r2), "r"(at + u), "r"(stop), "n"(QB * 4));
             }
+            wp = min(wp, wlim);
 #pragma unroll
             for (int u = 0; u < kSelChunk; ++u) asm volatile("" ::"f"(c[u].w));  // keep .w allocated (see above)
         };
@@ -473,7 +499,6 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
             pn = p + kSelChunk; endn = end; spn = sp;
             if (pn >= end && sp < nsp) { const int2 t = SP[sp * QB]; pn = t.x; endn = t.y; spn = sp + 1; }
         };
-        float4 ca[kSelChunk], cb[kSelChunk];
         fetch(ca, p, end);
         while (__any_sync(0xffffffffu, p < end)) {
             int pn, endn, spn;
@@ -498,8 +523,10 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
     // compares) and such a query is retried exactly by the general kernel -- about 0.5 % on uniform clouds,
     // every query on a lattice.  Otherwise ascending truncated keys ARE ascending (d2, position).
     static_assert(kSelectCap <= 128, "slot must fit the low key bits");
-    const bool searched = valid && cnt >= K_T && cnt <= kSelectCap;
-    const int have = searched ? cnt : 0;
+    asm volatile("" ::: "memory");  // the appends above were written behind the compiler's back
+    const int cnt = (int)((wp - wp0) / (QB * 4u)) - 1;  // candidates inside the sphere, the query itself not counted
+    const bool searched = valid && cnt >= K_T && wp < wlim;
+    const int have = searched ? cnt + 1 : 0;
     unsigned a[kSelectNet];
     for (int base = 0, round = 0; round == 0 || __any_sync(0xffffffffu, have > base); ++round) {
         // Later rounds keep the K_T + 1 smallest so far: the extra one guards the border -- whatever is
@@ -513,7 +540,8 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
                 a[u] = 0xFFFFFFFFu;
                 if (slot < have) {
                     const int pos = (int)BUF[slot * QB];
-                    a[u] = ((unsigned)(make_key(__ldg(P.pts + pos), s, pos) >> 32) & ~kSlotMask) | (unsigned)slot;
+                    const unsigned key = ((unsigned)(make_key(__ldg(P.pts + pos), s, pos) >> 32) & ~kSlotMask) | (unsigned)slot;
+                    a[u] = pos == q ? 0xFFFFFFFFu : key;
                 }
             }
         }
@@ -692,7 +720,7 @@ cudaError_t launch(const QueryParams &P, bool fast, cudaStream_t st) {
     constexpr bool kHasSelect = K_T == 8 || K_T == 20 || K_T == 32 || K_T == 50;
     if (fast && kHasSelect && P.use_select) {
         if constexpr (kHasSelect) {
-            constexpr int NET = K_T <= 20 ? 32 : 64, CAP = K_T <= 20 ? 52 : 96;  // 52: the most that still lets 6 blocks share an SM
+            constexpr int NET = K_T <= 20 ? 32 : 64, CAP = K_T <= 20 ? 56 : 100;  // 56: the most that still lets 6 blocks share an SM (6 x 38 KB = 228 KB)
             const size_t smem = (sizeof(unsigned) * CAP + sizeof(int2) * kSpanSlots) * QB;
             e = cudaFuncSetAttribute(kn_query_select_kernel<K_T, QB, NET, CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)smem);
