@@ -392,13 +392,14 @@ __global__ void __launch_bounds__(QB) kn_query_fast_kernel(const __grid_constant
 constexpr int kSelChunk = KN_SEL_CHUNK;  // candidates a lane takes per lock-step iteration
 
 // c[U] = src[U] for every U < kSelChunk with at + U < stop, as predicated 16-byte loads at immediate offsets
-// from one base address; records that are not loaded keep their old register contents.
+// from one base address.  A record that is not loaded is left UNDEFINED (whatever its registers held): the
+// operands are declared write-only so that the buffers are not live -- 32 registers -- outside the scan loop.
 template <int U>
 __device__ __forceinline__ void load_records_if(float4 (&c)[kSelChunk], int at, int stop, const float4 *src) {
     if constexpr (U < kSelChunk) {
         asm("{\n\t.reg .pred p;\n\tsetp.lt.s32 p, %4, %5;\n\t"
             "@p ld.global.nc.v4.f32 {%0, %1, %2, %3}, [%6+%7];\n\t}"
-            : "+f"(c[U].x), "+f"(c[U].y), "+f"(c[U].z), "+f"(c[U].w)
+            : "=f"(c[U].x), "=f"(c[U].y), "=f"(c[U].z), "=f"(c[U].w)
             : "r"(at + U), "r"(stop), "l"(src), "n"(16 * U));
         load_records_if<U + 1>(c, at, stop, src);
     }
@@ -427,9 +428,6 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
     const unsigned wp0 = (unsigned)__cvta_generic_to_shared(BUF);
     const unsigned wlim = wp0 + (unsigned)(kSelectCap - kSelChunk) * QB * 4u;
     unsigned wp = wp0;
-    float4 ca[kSelChunk], cb[kSelChunk];  // the two record buffers of the pipelined scan (see below)
-#pragma unroll
-    for (int u = 0; u < kSelChunk; ++u) ca[u] = cb[u] = make_float4(0.f, 0.f, 0.f, 0.f);
 
     // ---- search the sphere: rows in batches, spans first, then a lock-step stream over them -----------------
     for (int e0 = 0, e1 = min(kFirstBatch, P.tab.n); e0 < P.tab.n && P.tab.lb2[e0] <= r2;
@@ -475,7 +473,7 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
         // zeroed the four destination registers before every predicated load and spent seven instructions
         // on "if (pass) BUF[min(cnt, cap)] = i; cnt += pass" (select 0/1, add, clamp, multiply-add, store):
         // 23 instructions per candidate in all, in a kernel that is bound by instruction issue.  A record that
-        // is not loaded keeps stale values, which is harmless: the append tests the same index bound again.
+        // is not loaded holds stale values, which is harmless: the append tests the same index bound again.
         auto fetch = [&](float4(&c)[kSelChunk], int at, int stop) {
             load_records_if<0>(c, at, stop, P.pts + at);
         };
@@ -499,6 +497,7 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
             pn = p + kSelChunk; endn = end; spn = sp;
             if (pn >= end && sp < nsp) { const int2 t = SP[sp * QB]; pn = t.x; endn = t.y; spn = sp + 1; }
         };
+        float4 ca[kSelChunk], cb[kSelChunk];
         fetch(ca, p, end);
         while (__any_sync(0xffffffffu, p < end)) {
             int pn, endn, spn;
