@@ -29,7 +29,7 @@ C_ABI_SYMBOLS = [
     "knc_get_knearests", "knc_get_knearests_original", "knc_get_stats", "knc_get_info", "knc_get_timings",
     "knc_grid_dim", "knc_last_error", "knc_version", "knc_generate_uniform_device", "knc_scan_cells_noalloc",
     "knc_slab_route", "knc_get_knearests_global", "knc_set_index_offset", "knc_get_permutation_global",
-    "knc_get_dists", "knc_query_points",
+    "knc_get_dists", "knc_query_points", "knc_get_tags",
     "knc_route_begin", "knc_route_scatter", "knc_route_end",
     "knc_peer_alloc", "knc_peer_open", "knc_peer_close", "knc_peer_free",
 ]
@@ -119,6 +119,7 @@ def lib() -> C.CDLL:
         L.knc_peer_free.argtypes = [vp]
         L.knc_set_index_offset.argtypes = [vp, C.c_longlong]
         L.knc_get_permutation_global.argtypes = [vp, vp, C.c_int, vp]
+        L.knc_get_tags.argtypes = [vp, C.POINTER(vp)]
         L.knc_last_error.restype = C.c_char_p
         L.knc_version.restype = C.c_char_p
         _lib = L
@@ -143,7 +144,7 @@ class KnProblem:
 
     ``points`` is either a host array (anything numpy can view as float32 [n,3]; copied to the device,
     as kn_prepare does, knearests.cu:308-311) or a CUDA ``torch.Tensor`` float32 [n,3] (used in place);
-    a CUDA tensor [n,4] is read as 16-byte records x, y, z, ignored word (knc_options.point_stride = 4).
+    a CUDA tensor [n,4] is read as 16-byte records x, y, z, tag (knc_options.point_stride = 4; see tags_ptr).
     """
 
     def __init__(self, points, k: int = 0, density: float = 0.0, grid_dim: int = 0, slab=None,
@@ -197,6 +198,12 @@ class KnProblem:
         out = np.empty((self.info.query_count, self.info.k), np.float32)
         _check(lib().knc_get_dists(self._h, out.ctypes.data))
         return out
+
+    def tags_ptr(self) -> int:
+        """Device address of the input records' 4th words in sorted order (knc_get_tags; [n, 4] input only)."""
+        ptr = C.c_void_p()
+        _check(lib().knc_get_tags(self._h, C.byref(ptr)))
+        return int(ptr.value)
 
     def query_points(self, xyz, with_d2: bool = False):
         """kNN of points that are not in the cloud (kd_tree.cpp:168-192 semantics)."""

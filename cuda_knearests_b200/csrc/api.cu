@@ -106,7 +106,7 @@ int default_k() {
 void free_device_state(knc_problem *p) {
     cudaStream_t st = p->stream;
     void *ptrs[] = {p->pub.d_cell_max, p->pub.d_permutation, p->pub.d_counters, p->pub.d_ptrs,
-                    p->pub.d_globcounter, p->pub.d_stored_points, p->pub.d_knearests, p->d_points4, p->d_diag};
+                    p->pub.d_globcounter, p->pub.d_stored_points, p->pub.d_knearests, p->d_points4, p->d_diag, p->d_tags};
     for (void *q : ptrs)
         if (q) cudaFreeAsync(q, st);
     if (st) {
@@ -210,6 +210,7 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     CU(dev_alloc((void **)&p->pub.d_permutation, sizeof(unsigned) * (size_t)n, st));
     CU(dev_alloc((void **)&p->pub.d_stored_points, sizeof(float) * 3 * (size_t)n, st));
     CU(dev_alloc((void **)&p->d_points4, sizeof(float4) * (size_t)n, st));
+    if (stride == 4) CU(dev_alloc((void **)&p->d_tags, sizeof(unsigned) * (size_t)n, st));
     // temporaries of the build
     s.tile_count = kn_build_scratch_tiles(cells);
     CU(dev_alloc((void **)&s.d_cellid, sizeof(int) * (size_t)n, st));
@@ -220,6 +221,7 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     if (n >= KN_BIN_MIN_POINTS && o.algorithm != 3) {  // algorithm 3: build without the z-band pre-pass (A/B, tests)
         CU(dev_alloc((void **)&s.d_bin_recs, sizeof(float4) * (size_t)n, st));
         CU(dev_alloc((void **)&s.d_bin_counts, sizeof(int) * kn_bin_counts_ints(n), st));
+        if (stride == 4) CU(dev_alloc((void **)&s.d_bin_tags, sizeof(unsigned) * (size_t)n, st));
     }
 
     CU(cudaEventRecord(p->ev[0], st));
@@ -232,7 +234,7 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     g.D = D; g.zb = zb; g.ze = ze; g.Df = (float)D; g.w = 1000.f / (float)D; g.invw = (float)D / 1000.f;
     CU(cudaEventRecord(p->ev[1], st));
     CU(kn_launch_build(d_in, stride, n, g, cells, p->pub.d_counters, p->pub.d_ptrs, p->pub.d_globcounter,
-                       p->pub.d_permutation, (float *)p->pub.d_stored_points, p->d_points4, s, st));
+                       p->pub.d_permutation, (float *)p->pub.d_stored_points, p->d_points4, p->d_tags, s, st));
     CU(cudaEventRecord(p->ev[2], st));
     CU(cudaMemsetAsync(p->pub.d_cell_max, 0, sizeof(float), st));
     {   // the queries are the points of the owned planes: one contiguous run of sorted positions
@@ -256,7 +258,7 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
 out:
     if (!o.points_on_device && d_in) cudaFreeAsync(d_in, st);
     {
-        void *tmp[] = {s.d_cellid, s.d_rank, s.d_tile, s.d_ticket, s.d_biglist, s.d_bin_recs, s.d_bin_counts};
+        void *tmp[] = {s.d_cellid, s.d_rank, s.d_tile, s.d_ticket, s.d_biglist, s.d_bin_recs, s.d_bin_counts, s.d_bin_tags};
         for (void *q : tmp)
             if (q) cudaFreeAsync(q, st);
     }
@@ -473,6 +475,13 @@ int knc_get_knearests_original(knc_problem *p, unsigned int *out_neighbors) {
 out:
     if (d_tmp) cudaFreeAsync(d_tmp, p->stream);
     return rc;
+}
+
+int knc_get_tags(knc_problem *p, const unsigned int **d_tags) {
+    if (!p || !d_tags) return fail(KNC_ERR_INVALID, "knc_get_tags: NULL argument");
+    if (!p->d_tags) return fail(KNC_ERR_STATE, "knc_get_tags: the handle was prepared with point_stride 3 (no 4th word)");
+    *d_tags = p->d_tags;
+    return KNC_OK;
 }
 
 int knc_get_stats(knc_problem *p, knc_stats *out) {

@@ -35,6 +35,12 @@ __device__ __forceinline__ int axis_cell(float p, float Df, int lo, int hi) {
     return max(lo, min(c, hi));
 }
 
+// one input record: a single 16-byte load for aligned 4-float records, else three scalars (4th word = 0)
+__device__ __forceinline__ float4 load_record(const float *rec, bool vec4) {
+    if (vec4) return __ldg(reinterpret_cast<const float4 *>(rec));
+    return make_float4(__ldg(rec), __ldg(rec + 1), __ldg(rec + 2), 0.f);
+}
+
 // ---------------------------------------------------------------------------------------- count
 // One point per thread; a block stages its 256 points (768 floats) through shared memory with
 // float4 loads, so global reads are 16-byte vectorised and fully coalesced although the input is AoS.
@@ -404,19 +410,22 @@ __global__ void __launch_bounds__(1024) kn_bin_scan_kernel(int *blockcounts, int
 
 __global__ void __launch_bounds__(kBinThreads)
 kn_bin_scatter_kernel(const float *__restrict__ xyz, int stride, int n, GridGeom g, int planes_per_bin, int nblocks,
-                      const int *__restrict__ offsets, const int *__restrict__ totals, float4 *__restrict__ recs) {
+                      const int *__restrict__ offsets, const int *__restrict__ totals, float4 *__restrict__ recs,
+                      unsigned int *__restrict__ tags, int vec4) {  // tags: 4th input words in banded order (stride 4) or NULL
     __shared__ int s_cnt[kBinGroups + 1][kBins];
     __shared__ int s_base[kBins];
     const long long base = (long long)blockIdx.x * kBinTile + threadIdx.x;
     float x[kBinItems], y[kBinItems], z[kBinItems];
+    unsigned tag[kBinItems];
     bool valid[kBinItems];
     int bin[kBinItems], before[kBinItems];
 #pragma unroll
     for (int r = 0; r < kBinItems; ++r) {
         const long long i = base + (long long)r * kBinThreads;
         valid[r] = i < n;
-        const float *rec = xyz + (valid[r] ? i : 0) * stride;
-        x[r] = __ldg(rec); y[r] = __ldg(rec + 1); z[r] = __ldg(rec + 2);
+        const float4 v = load_record(xyz + (valid[r] ? i : 0) * stride, vec4);
+        x[r] = v.x; y[r] = v.y; z[r] = v.z;
+        tag[r] = __float_as_uint(v.w);
     }
     if (threadIdx.x < kBins) {  // first record of each band (the totals of the lower bands) + this tile's start inside it
         int b = 0;
@@ -428,15 +437,18 @@ kn_bin_scatter_kernel(const float *__restrict__ xyz, int stride, int n, GridGeom
     bin_ranks_in_tile(bin, valid, before, s_cnt);  // contains the barriers that publish s_base
 #pragma unroll
     for (int r = 0; r < kBinItems; ++r)
-        if (valid[r])
-            recs[s_base[bin[r]] + before[r]] =
-                make_float4(x[r], y[r], z[r], __uint_as_float((unsigned)(base + (long long)r * kBinThreads)));
+        if (valid[r]) {
+            const int pos = s_base[bin[r]] + before[r];
+            recs[pos] = make_float4(x[r], y[r], z[r], __uint_as_float((unsigned)(base + (long long)r * kBinThreads)));
+            if (tags) tags[pos] = tag[r];
+        }
 }
 
 // --------------------------------------------------------------------------------------- gather
 __global__ void __launch_bounds__(kBuildThreads)
 kn_gather_kernel(const float *__restrict__ xyz, int stride, int n, unsigned int *__restrict__ permutation,
-                 float *__restrict__ points3, float4 *__restrict__ points4, int binned) {
+                 float *__restrict__ points3, float4 *__restrict__ points4, int binned,
+                 const unsigned int *__restrict__ bin_tags, unsigned int *__restrict__ tags, int vec4) {
     __shared__ float tile[kBuildThreads * 3];
     const int tid = threadIdx.x;
     const long long first = (long long)blockIdx.x * kBuildThreads;
@@ -445,9 +457,12 @@ kn_gather_kernel(const float *__restrict__ xyz, int stride, int n, unsigned int 
     if (s < n) {
         unsigned i = permutation[s];
         const float *rec = xyz + (long long)stride * i;
-        const float x = __ldg(rec), y = __ldg(rec + 1), z = __ldg(rec + 2);
+        const float4 v = load_record(rec, vec4);
+        const float x = v.x, y = v.y, z = v.z;
+        // the caller's 4th word travels with the point (stride-4 input): a multi-GPU caller keeps global ids there
+        if (tags) tags[s] = binned ? __ldg(bin_tags + i) : __float_as_uint(v.w);
         if (binned) {  // `i` was a position in the binned records; their 4th word is the original index
-            i = __float_as_uint(__ldg(rec + 3));
+            i = __float_as_uint(v.w);
             permutation[s] = i;
         }
         points4[s] = make_float4(x, y, z, __uint_as_float(i));
@@ -495,8 +510,9 @@ size_t kn_build_scratch_tiles(long long cells) { return (size_t)((cells + kScanT
 
 cudaError_t kn_launch_build(const float *d_in_xyz, int stride, int n, const GridGeom &g, long long cells, int *d_counters,
                             int *d_ptrs, int *d_globcounter, unsigned int *d_permutation, float *d_points3,
-                            float4 *d_points4, const BuildScratch &s, cudaStream_t st) {
+                            float4 *d_points4, unsigned int *d_tags, const BuildScratch &s, cudaStream_t st) {
     cudaError_t e;
+    if (d_tags && stride != 4) return cudaErrorInvalidValue;  // tags are the 4th word of 16-byte input records
     if ((e = cudaMemsetAsync(d_counters, 0, sizeof(int) * (size_t)cells, st)) != cudaSuccess) return e;
     if ((e = cudaMemsetAsync(s.d_tile, 0, sizeof(unsigned long long) * s.tile_count, st)) != cudaSuccess) return e;
     if ((e = cudaMemsetAsync(s.d_ticket, 0, sizeof(int) * 2, st)) != cudaSuccess) return e;
@@ -509,7 +525,9 @@ cudaError_t kn_launch_build(const float *d_in_xyz, int stride, int n, const Grid
         kn_bin_count_kernel<<<nblocks, kBinThreads, 0, st>>>(d_in_xyz, stride, n, g, planes_per_bin, nblocks, s.d_bin_counts);
         kn_bin_scan_kernel<<<kBins, 1024, 0, st>>>(s.d_bin_counts, nblocks, s.d_bin_counts + (size_t)kBins * nblocks);
         kn_bin_scatter_kernel<<<nblocks, kBinThreads, 0, st>>>(d_in_xyz, stride, n, g, planes_per_bin, nblocks, s.d_bin_counts,
-                                                              s.d_bin_counts + (size_t)kBins * nblocks, s.d_bin_recs);
+                                                              s.d_bin_counts + (size_t)kBins * nblocks, s.d_bin_recs,
+                                                              d_tags ? s.d_bin_tags : nullptr,
+                                                              stride == 4 && ((uintptr_t)d_in_xyz & 15u) == 0);
         src = reinterpret_cast<const float *>(s.d_bin_recs);
         stride = 4;
         binned = 1;
@@ -525,7 +543,9 @@ cudaError_t kn_launch_build(const float *d_in_xyz, int stride, int n, const Grid
                                                                                s.d_ticket + 1, s.d_biglist);
     kn_order_big_kernel<<<148, 1024, 0, st>>>(s.d_ticket + 1, s.d_biglist, d_ptrs, d_permutation);
     kn_gather_kernel<<<blocks_for(n, kBuildThreads), kBuildThreads, 0, st>>>(src, stride, n, d_permutation,
-                                                                            d_points3, d_points4, binned);
+                                                                            d_points3, d_points4, binned,
+                                                                            binned ? s.d_bin_tags : nullptr, d_tags,
+                                                                            stride == 4 && aligned16);
     return cudaGetLastError();
 }
 

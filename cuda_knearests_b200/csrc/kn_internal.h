@@ -23,6 +23,7 @@ struct knc_problem {
     int query_begin, query_count;
     int solved;
     float4 *d_points4;           // [n] x, y, z, bits(original index): what the query kernel reads
+    unsigned int *d_tags;        // [n] 4th word of every input record in sorted order (point_stride 4 only, else NULL)
     unsigned int *d_diag;        // [4] restarts, max radius^2 bits, halo misses, spare
     cudaStream_t stream;
     cudaStream_t copy_stream;    // device->host row copies of knc_solve_to_host (created on first use)
@@ -49,13 +50,14 @@ struct BuildScratch {
     size_t tile_count;
     float4 *d_bin_recs;          // [n] z-banded copy of the input (large clouds only, else NULL)
     int *d_bin_counts;           // [kn_bin_counts_ints(n)] per-block band counts + band totals
+    unsigned int *d_bin_tags;    // [n] 4th input words in banded order (large clouds with point_stride 4, else NULL)
 };
 size_t kn_bin_counts_ints(int n);
 #define KN_BIN_MIN_POINTS 20000000  // below this the counters and records stay in L2 anyway (measured: no gain at 14 M)
 size_t kn_build_scratch_tiles(long long cells);
 cudaError_t kn_launch_build(const float *d_in_xyz, int stride, int n, const GridGeom &g, long long cells, int *d_counters,
                             int *d_ptrs, int *d_globcounter, unsigned int *d_permutation, float *d_points3,
-                            float4 *d_points4, const BuildScratch &s, cudaStream_t st);
+                            float4 *d_points4, unsigned int *d_tags, const BuildScratch &s, cudaStream_t st);
 cudaError_t kn_launch_generate(float *d_xyz, long long first, long long count, uint64_t seed, cudaStream_t st);
 cudaError_t kn_launch_remap_original(const unsigned int *d_knn, const unsigned int *d_perm, int n, int k,
                                      unsigned int *d_out, cudaStream_t st);

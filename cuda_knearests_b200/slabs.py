@@ -7,7 +7,7 @@ on either side as read-only candidates.  One exchange step moves the points:
 
   knc_slab_route (CUDA, stable multi-split by destination, 16-byte records)  ->  ONE all-to-all (NCCL
   over NVLink; gloo in the CPU tests)  ->  knc_prepare_ex(slab, point_stride 4) + knc_solve per rank
-  ->  rows in global sorted positions + knc_get_permutation_global
+  ->  rows in global sorted positions + the ids in sorted order (knc_get_tags) = the global permutation slice
 
 Because the route is stable and ranks hold rising index ranges, a rank receives its slab in global index
 order, the engine's stable cell sort reproduces the single-GPU order, and the rows are bit-identical to
@@ -264,11 +264,8 @@ def solve_distributed(local_xyz, first_id: int, n_total: int, k: int, group=None
                     p.solve()
                 mark("solve")
                 info.update(p.timings(), queries=p.info.query_count)
-                perm = torch.empty((p.info.query_count,), dtype=torch.int32, device=dev)
-                torch.cuda.current_stream().synchronize()
-                mark("permutation_alloc")
-                K._check(K.lib().knc_get_permutation_global(p._h, C.c_void_p(recv_xyz.data_ptr() + 12), 4,
-                                                            C.c_void_p(perm.data_ptr())))
+                # this rank's slice of the global permutation: the records' ids, carried through the build as tags
+                perm = torch.as_tensor(_DevView(p.tags_ptr() + 4 * p.info.query_begin, (p.info.query_count,)), device=dev)
                 mark("permutation_slice")
                 rows = torch.as_tensor(_DevView(p.info.d_knearests, (p.info.query_count, k)), device=dev)
             except K.KnError as e:
@@ -380,7 +377,7 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
         e2e = {"value": n / float(te.item()), "unit": UNIT, "h2d_bytes_per_step": 12 * n,
                "d2h_bytes_per_step": 4 * k * n + 4 * n, "ms_per_step": 1e3 * float(te.item()), "steps": e_steps,
                "call": "per rank: pinned host chunk -> device, route + all-to-all + knc_prepare_ex(slab) + knc_solve_to_host + "
-                       "knc_get_permutation_global; rows (global sorted positions) stream to pinned host memory during the solve "
+                       "knc_get_tags (permutation slice); rows (global sorted positions) stream to pinned host memory during the solve "
                        "(knc_solve_to_host), permutation slice copied after"}
 
     if rank == 0:
@@ -399,7 +396,7 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
         line = {"metric": METRIC, "value": n / (wall / args.steps), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
-                "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 15 * args.steps * world,  # per rank: route 3, build 6 (+3 z-band split when the slab is large), query 2, permutation slice 1
+                "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 14 * args.steps * world,  # per rank: route 3, build 6 (+3 z-band split when the slab is large), query 2
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": None, "kernel": "kn_query_select_kernel (slowest rank)",
                              "kernel_ms": float(allstats[worst][0].item()),

@@ -58,8 +58,8 @@ typedef struct {
     int algorithm;          /* 0 = automatic (select/insertion kernel + retry), 1 = general kernel only,
                                2 = insertion kernel for every k, 3 = grid build without the z-band
                                pre-pass (testing, A/B)                                                  */
-    int point_stride;       /* floats per input point: 3 (xyz, default) or 4 (xyz + one ignored word,
-                               e.g. the records knc_slab_route writes)                                  */
+    int point_stride;       /* floats per input point: 3 (xyz, default) or 4 (xyz + one word that is carried
+                               along, see knc_get_tags; e.g. the records knc_slab_route writes)         */
 } knc_options;
 
 /* What the handle holds; device pointers are valid until knc_free. */
@@ -144,6 +144,15 @@ int knc_get_dists(knc_problem *p, float *out_d2);
  * entry point.  Rows (HOST, m*k unsigned) hold sorted positions, ascending (d2, sorted position), nothing is
  * excluded; out_d2 (HOST, m*k floats) may be NULL.  Works on any prepared handle, solved or not. */
 int knc_query_points(knc_problem *p, const float *xyz, int m, unsigned int *out_knn, float *out_d2);
+
+/* The 4th word of every input record, in SORTED order (DEVICE pointer to allocated_points words, owned by the
+ * handle, valid until knc_free): tags[s] belongs to the point at sorted position s, the queries are
+ * tags[query_begin .. query_begin + query_count).  Only for handles prepared with point_stride = 4
+ * (KNC_ERR_STATE otherwise).  No counterpart in the reference (its input is float3, knearests.h:21): the
+ * multi-GPU caller keeps each point's GLOBAL id there, so this run IS its slice of the global permutation --
+ * gathered during the build, where the record is being read anyway, instead of by a random gather afterwards
+ * (knc_get_permutation_global). */
+int knc_get_tags(knc_problem *p, const unsigned int **d_tags);
 
 /* Replaces kn_print_stats (knearests.h:29, knearests.cu:440-466), as data. */
 int knc_get_stats(knc_problem *p, knc_stats *out);

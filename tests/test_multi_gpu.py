@@ -72,6 +72,9 @@ def test_emulated_ranks_reproduce_single_gpu_rows(kn, oracle, world, k, n):
             torch.cuda.synchronize()
             kn._check(kn.lib().knc_get_permutation_global(p._h, ids_ptr, 4, C.c_void_p(perm.data_ptr())))
             got_perm.append(perm.cpu().numpy().view(np.uint32))
+            # the same slice without a gather: the ids travelled through the build as tags (knc_get_tags)
+            tags = torch.as_tensor(slabs._DevView(p.tags_ptr() + 4 * p.info.query_begin, (nq,)), device="cuda")
+            assert torch.equal(tags, perm)
             base += nq
     assert base == n                                            # every point is a query of exactly one rank
     assert np.array_equal(np.concatenate(got_perm), want_perm)  # global permutation, slice by slice
