@@ -35,10 +35,10 @@ __device__ __forceinline__ int axis_cell(float p, float Df, int lo, int hi) {
     return max(lo, min(c, hi));
 }
 
-// one input record: a single 16-byte load for aligned 4-float records, else three scalars (4th word = 0)
-__device__ __forceinline__ float4 load_record(const float *rec, bool vec4) {
+// one input record: a single 16-byte load for aligned 4-float records, else scalars (4th word = 0 for xyz input)
+__device__ __forceinline__ float4 load_record(const float *rec, int stride, bool vec4) {
     if (vec4) return __ldg(reinterpret_cast<const float4 *>(rec));
-    return make_float4(__ldg(rec), __ldg(rec + 1), __ldg(rec + 2), 0.f);
+    return make_float4(__ldg(rec), __ldg(rec + 1), __ldg(rec + 2), stride == 4 ? __ldg(rec + 3) : 0.f);
 }
 
 // ---------------------------------------------------------------------------------------- count
@@ -423,7 +423,7 @@ kn_bin_scatter_kernel(const float *__restrict__ xyz, int stride, int n, GridGeom
     for (int r = 0; r < kBinItems; ++r) {
         const long long i = base + (long long)r * kBinThreads;
         valid[r] = i < n;
-        const float4 v = load_record(xyz + (valid[r] ? i : 0) * stride, vec4);
+        const float4 v = load_record(xyz + (valid[r] ? i : 0) * stride, stride, vec4);
         x[r] = v.x; y[r] = v.y; z[r] = v.z;
         tag[r] = __float_as_uint(v.w);
     }
@@ -457,7 +457,7 @@ kn_gather_kernel(const float *__restrict__ xyz, int stride, int n, unsigned int 
     if (s < n) {
         unsigned i = permutation[s];
         const float *rec = xyz + (long long)stride * i;
-        const float4 v = load_record(rec, vec4);
+        const float4 v = load_record(rec, stride, vec4);
         const float x = v.x, y = v.y, z = v.z;
         // the caller's 4th word travels with the point (stride-4 input): a multi-GPU caller keeps global ids there
         if (tags) tags[s] = binned ? __ldg(bin_tags + i) : __float_as_uint(v.w);

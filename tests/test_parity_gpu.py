@@ -301,6 +301,33 @@ def test_slab_mode_rows_equal_whole_grid_rows(kn, oracle):
         assert np.array_equal(np.nonzero(keep)[0][perm], g.permutation[base: base + sub.shape[0]])
 
 
+def test_fourth_word_of_16_byte_records_is_carried_into_sorted_order(kn, oracle):
+    """knc_get_tags (no reference counterpart): [n, 4] device records x, y, z, tag  ->  tags[s] = tag of the point at
+    sorted position s, i.e. tag_in[permutation[s]]; aligned and unaligned record arrays, with and without the
+    z-band pre-pass; xyz input has no tags."""
+    import torch
+    from cuda_knearests_b200 import slabs
+    n = 300_000
+    pts = oracle.generate_uniform(n, seed=5)
+    tag = np.random.default_rng(5).integers(0, 2**32, n, dtype=np.uint32)
+    rec = np.empty((n, 4), np.float32)
+    rec[:, :3] = pts
+    rec[:, 3] = tag.view(np.float32)
+    flat = torch.zeros(4 * n + 1, dtype=torch.float32, device="cuda")
+    for shift in (0, 1):  # 1: records start 4 bytes off a 16-byte boundary
+        view = flat[shift: shift + 4 * n].view(n, 4)
+        view.copy_(torch.from_numpy(rec))
+        with kn.KnProblem(view, k=8) as p:
+            perm = p.get_permutation()
+            got = torch.as_tensor(slabs._DevView(p.tags_ptr(), (n,)), device="cuda").cpu().numpy().view(np.uint32)
+            assert np.array_equal(got, tag[perm])
+            assert np.array_equal(p.get_points(), pts[perm])
+    with kn.KnProblem(torch.from_numpy(pts).cuda(), k=8) as p:
+        with pytest.raises(kn.KnError) as e:
+            p.tags_ptr()
+        assert e.value.code == 4  # KNC_ERR_STATE
+
+
 def test_slab_mode_reports_insufficient_halo(kn, oracle):
     pts = oracle.generate_uniform(100_000, seed=3)
     D = oracle.grid_dim(len(pts))
