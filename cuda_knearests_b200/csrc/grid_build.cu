@@ -435,13 +435,41 @@ kn_bin_scatter_kernel(const float *__restrict__ xyz, int stride, int n, GridGeom
 #pragma unroll
     for (int r = 0; r < kBinItems; ++r) bin[r] = bin_of_z(z[r], g, planes_per_bin);
     bin_ranks_in_tile(bin, valid, before, s_cnt);  // contains the barriers that publish s_base
+    // The records leave through shared memory in tile-sorted order (band by band): a warp then writes one
+    // contiguous run of 512 bytes instead of 32 half-sectors in ~25 different bands.
+    extern __shared__ float4 s_stage[];          // [kBinTile]
+    __shared__ unsigned char s_band[kBinTile];   // band of each staged slot
+    __shared__ int s_first[kBins];               // first staged slot of each band
+    if (threadIdx.x < 32) {                      // exclusive scan of the tile's 64 band counts, two per lane
+        const int lane = threadIdx.x;
+        const int c0 = s_cnt[kBinGroups][2 * lane], c1 = s_cnt[kBinGroups][2 * lane + 1];
+        int incl = c0 + c1;
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
+        }
+        s_first[2 * lane] = incl - c0 - c1;
+        s_first[2 * lane + 1] = incl - c1;
+    }
+    __syncthreads();
 #pragma unroll
     for (int r = 0; r < kBinItems; ++r)
         if (valid[r]) {
-            const int pos = s_base[bin[r]] + before[r];
-            recs[pos] = make_float4(x[r], y[r], z[r], __uint_as_float((unsigned)(base + (long long)r * kBinThreads)));
-            if (tags) tags[pos] = tag[r];
+            const int slot = s_first[bin[r]] + before[r];
+            s_stage[slot] = make_float4(x[r], y[r], z[r], __uint_as_float((unsigned)(base + (long long)r * kBinThreads)));
+            s_band[slot] = (unsigned char)bin[r];
+            if (tags) tags[s_base[bin[r]] + before[r]] = tag[r];
         }
+    __syncthreads();
+    const int here = (int)min((long long)kBinTile, (long long)n - (long long)blockIdx.x * kBinTile);
+#pragma unroll
+    for (int r = 0; r < kBinItems; ++r) {
+        const int slot = r * kBinThreads + threadIdx.x;
+        if (slot < here) {
+            const int b = s_band[slot];
+            recs[s_base[b] + slot - s_first[b]] = s_stage[slot];
+        }
+    }
 }
 
 // --------------------------------------------------------------------------------------- gather
@@ -524,7 +552,9 @@ cudaError_t kn_launch_build(const float *d_in_xyz, int stride, int n, const Grid
         const int nblocks = (int)blocks_for(n, kBinTile);
         kn_bin_count_kernel<<<nblocks, kBinThreads, 0, st>>>(d_in_xyz, stride, n, g, planes_per_bin, nblocks, s.d_bin_counts);
         kn_bin_scan_kernel<<<kBins, 1024, 0, st>>>(s.d_bin_counts, nblocks, s.d_bin_counts + (size_t)kBins * nblocks);
-        kn_bin_scatter_kernel<<<nblocks, kBinThreads, 0, st>>>(d_in_xyz, stride, n, g, planes_per_bin, nblocks, s.d_bin_counts,
+        if ((e = cudaFuncSetAttribute(kn_bin_scatter_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      (int)(sizeof(float4) * kBinTile))) != cudaSuccess) return e;
+        kn_bin_scatter_kernel<<<nblocks, kBinThreads, sizeof(float4) * kBinTile, st>>>(d_in_xyz, stride, n, g, planes_per_bin, nblocks, s.d_bin_counts,
                                                               s.d_bin_counts + (size_t)kBins * nblocks, s.d_bin_recs,
                                                               d_tags ? s.d_bin_tags : nullptr,
                                                               stride == 4 && ((uintptr_t)d_in_xyz & 15u) == 0);
