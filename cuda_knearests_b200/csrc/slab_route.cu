@@ -42,19 +42,36 @@ __device__ __forceinline__ unsigned dest_mask(int plane, const RoutePlan &pl) {
     return m;
 }
 
-// per block and destination: how many of the block's points go there.  counts[d * nblocks + block]
+// A block takes a TILE of kRouteTile consecutive points, kRouteItems per thread, all loaded before the first
+// barrier (one point per thread left the kernels waiting on a single load per barrier, 5-8x off the HBM time).
+// Item r of thread t is point  tile*kRouteTile + r*kRouteThreads + t,  so the warp-sized run  v = r*8 + warp
+// precedes run v + 1 in input order.
+constexpr int kRouteItems = 4;
+constexpr int kRouteTile = kRouteThreads * kRouteItems;
+constexpr int kRouteRuns = kRouteItems * (kRouteThreads / 32);
+
+// per tile and destination: how many of the tile's points go there.  counts[d * nblocks + tile]
 __global__ void __launch_bounds__(kRouteThreads)
 kn_route_count_kernel(const float *__restrict__ xyz, int n, float Df, int D, const __grid_constant__ RoutePlan pl,
                       int nblocks, int *__restrict__ counts) {
     __shared__ int s_cnt[kMaxRanks];
     const int tid = threadIdx.x;
     if (tid < kMaxRanks) s_cnt[tid] = 0;
+    const long long base = (long long)blockIdx.x * kRouteTile + tid;
+    float z[kRouteItems];
+#pragma unroll
+    for (int r = 0; r < kRouteItems; ++r) {
+        const long long i = base + (long long)r * kRouteThreads;
+        z[r] = i < n ? __ldg(xyz + 3 * i + 2) : 0.f;
+    }
     __syncthreads();
-    const long long i = (long long)blockIdx.x * kRouteThreads + tid;
-    const unsigned m = i < n ? dest_mask(plane_of(__ldg(xyz + 3 * i + 2), Df, D), pl) : 0u;
-    for (int d = 0; d < pl.nranks; ++d) {
-        const unsigned b = __ballot_sync(0xffffffffu, (m >> d) & 1u);
-        if ((tid & 31) == 0 && b) atomicAdd(&s_cnt[d], __popc(b));
+#pragma unroll
+    for (int r = 0; r < kRouteItems; ++r) {
+        const unsigned m = base + (long long)r * kRouteThreads < n ? dest_mask(plane_of(z[r], Df, D), pl) : 0u;
+        for (int d = 0; d < pl.nranks; ++d) {
+            const unsigned b = __ballot_sync(0xffffffffu, (m >> d) & 1u);
+            if ((tid & 31) == 0 && b) atomicAdd(&s_cnt[d], __popc(b));
+        }
     }
     __syncthreads();
     if (tid < pl.nranks) counts[(size_t)tid * nblocks + blockIdx.x] = s_cnt[tid];
@@ -95,34 +112,64 @@ struct RouteDest {
     long long first[kMaxRanks];
 };
 
-// stable scatter: position = first[d] + block offset + rank among the block's earlier points
+// stable scatter: position = first[d] + tile offset + rank among the tile's earlier points
 __global__ void __launch_bounds__(kRouteThreads)
 kn_route_scatter_kernel(const float *__restrict__ xyz, int n, unsigned first_id, float Df, int D,
                         const __grid_constant__ RoutePlan pl, int nblocks, const int *__restrict__ offsets,
                         const __grid_constant__ RouteDest dst) {
-    __shared__ int s_warp[kMaxRanks][kRouteThreads / 32];
+    __shared__ int s_run[kMaxRanks][kRouteRuns];      // per destination: count of each run, then its exclusive prefix
+    __shared__ int s_part[kMaxRanks][kRouteRuns / 4];
+    static_assert(kMaxRanks * (kRouteRuns / 4) == kRouteThreads, "one thread per (destination, 4 runs)");
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const long long i = (long long)blockIdx.x * kRouteThreads + tid;
-    float x = 0.f, y = 0.f, z = 0.f;
-    unsigned m = 0;
-    if (i < n) {
-        x = __ldg(xyz + 3 * i); y = __ldg(xyz + 3 * i + 1); z = __ldg(xyz + 3 * i + 2);
-        m = dest_mask(plane_of(z, Df, D), pl);
+    const long long base = (long long)blockIdx.x * kRouteTile + tid;
+    float x[kRouteItems], y[kRouteItems], z[kRouteItems];
+    unsigned m[kRouteItems];
+#pragma unroll
+    for (int r = 0; r < kRouteItems; ++r) {
+        const long long i = base + (long long)r * kRouteThreads;
+        const long long j = i < n ? i : 0;
+        x[r] = __ldg(xyz + 3 * j); y[r] = __ldg(xyz + 3 * j + 1); z[r] = __ldg(xyz + 3 * j + 2);
+        m[r] = i < n ? dest_mask(plane_of(z[r], Df, D), pl) : 0u;
     }
-    for (int d = 0; d < pl.nranks; ++d) {
-        const unsigned b = __ballot_sync(0xffffffffu, (m >> d) & 1u);
-        if (lane == 0) s_warp[d][warp] = __popc(b);
-    }
+#pragma unroll
+    for (int r = 0; r < kRouteItems; ++r)
+        for (int d = 0; d < pl.nranks; ++d) {
+            const unsigned b = __ballot_sync(0xffffffffu, (m[r] >> d) & 1u);
+            if (lane == 0) s_run[d][r * (kRouteThreads / 32) + warp] = __popc(b);
+        }
     __syncthreads();
-    for (int d = 0; d < pl.nranks; ++d) {
-        const unsigned b = __ballot_sync(0xffffffffu, (m >> d) & 1u);
-        if ((m >> d) & 1u) {
-            int before = __popc(b & ((1u << lane) - 1u));
-            for (int wq = 0; wq < warp; ++wq) before += s_warp[d][wq];
-            const long long pos = dst.first[d] + offsets[(size_t)d * nblocks + blockIdx.x] + before;
-            dst.buf[d][pos] = make_float4(x, y, z, __uint_as_float(first_id + (unsigned)i));  // one 16-byte store
+    {   // exclusive prefix over the runs of each destination: thread (d, 4 runs) scans its part, then adds the parts below
+        const int d = tid / (kRouteRuns / 4), part = tid % (kRouteRuns / 4);
+        int run = 0;
+        if (d < pl.nranks) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int c = s_run[d][part * 4 + j];
+                s_run[d][part * 4 + j] = run;
+                run += c;
+            }
+        }
+        s_part[d][part] = run;
+        __syncthreads();
+        if (d < pl.nranks) {
+            int below = 0;
+            for (int q = 0; q < part; ++q) below += s_part[d][q];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) s_run[d][part * 4 + j] += below;
         }
     }
+    __syncthreads();
+#pragma unroll
+    for (int r = 0; r < kRouteItems; ++r)
+        for (int d = 0; d < pl.nranks; ++d) {
+            const unsigned b = __ballot_sync(0xffffffffu, (m[r] >> d) & 1u);
+            if ((m[r] >> d) & 1u) {
+                const int before = __popc(b & ((1u << lane) - 1u)) + s_run[d][r * (kRouteThreads / 32) + warp];
+                const long long pos = dst.first[d] + offsets[(size_t)d * nblocks + blockIdx.x] + before;
+                dst.buf[d][pos] = make_float4(x[r], y[r], z[r],  // one 16-byte store
+                                              __uint_as_float(first_id + (unsigned)(base + (long long)r * kRouteThreads)));
+            }
+        }
 }
 
 // rows[r*k + j] = ids[perm[knn[r*k + j]]], query_ids[r] = ids[perm[query_begin + r]]
@@ -195,7 +242,7 @@ extern "C" int knc_route_begin(const float *d_xyz, int n, unsigned int first_id,
         if (zsplit[d] == zsplit[d + 1]) r->pl.lo[d] = r->pl.hi[d] = 0;  // an empty slab wants nothing
         out_counts[d] = 0;
     }
-    r->nblocks = (n + kRouteThreads - 1) / kRouteThreads;
+    r->nblocks = (n + kRouteTile - 1) / kRouteTile;
     cudaError_t e = cudaSuccess;
     if (n > 0) {
         cudaStream_t st = 0;
