@@ -53,12 +53,17 @@ def parse():
     ap.add_argument("--cpu-sample", type=int, default=16_000_000, help="points of the CPU baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--density", type=float, default=1.0,
-                    help="points per grid cell handed to knc_prepare_ex (library default: the reference's 3.1; "
-                         "1.0 is ~14 %% faster on B200, profiles/r1_notes.md)")
+    ap.add_argument("--density", type=float, default=0.0,
+                    help="points per grid cell handed to knc_prepare_ex (library default: the reference's 3.1); "
+                         "0 = cuda_knearests_b200.fast_density(k): 1.0 at k=20, ~14 %% faster on B200 than 3.1, "
+                         "profiles/r1_notes.md")
     ap.add_argument("--algorithm", type=int, default=0, help="knc_options.algorithm (0 auto, 1 general, 2 insertion kernel)")
     ap.add_argument("--no-ref-gpu", action="store_true", help="skip timing the reference's own knearests.cu on this GPU")
-    return ap.parse_args()
+    args = ap.parse_args()
+    if args.density <= 0:
+        from cuda_knearests_b200 import fast_density
+        args.density = fast_density(args.k)
+    return args
 
 
 def measured_peak_gbs():

@@ -41,6 +41,18 @@ CXX_ABI_SYMBOLS = [
 ]
 
 
+def fast_density(k: int) -> float:
+    """Points per grid cell at which the query kernels run fastest on B200 for uniform clouds (measured at 100 M
+    points, profiles/r1_notes.md): the first search radius -- a sphere expected to hold k + 2.5 sqrt(k) + 2 points,
+    knn_query.cu -- should stay just under 2 cell widths, so that rows three cells away never enter the row table.
+    1.0 / 1.0 / 1.5 / 2.1 for k = 8 / 20 / 32 / 50.  The library default remains the reference's 3.1
+    (knearests.cu:249); the choice changes speed, never results."""
+    import math
+    lam = k + 2.5 * math.sqrt(k) + 2.0
+    cells_in_radius_2 = 4.0 / 3.0 * math.pi * 8.0
+    return max(1.0, math.ceil(1.005 * lam / cells_in_radius_2 * 10.0 - 1e-9) / 10.0)
+
+
 class KnError(RuntimeError):
     def __init__(self, code: int, message: str):
         super().__init__(f"knearests_b200 error {code}: {message}")

@@ -68,3 +68,15 @@ def test_argument_errors_are_reported_not_fatal(kn):
     assert L.knc_free(None) == 0
     with pytest.raises(kn.KnError):
         kn.KnProblem(pts, k=8, slab=(0, 4, 1, 3))  # slab without grid_dim
+
+
+def test_bench_grid_density_rule():
+    """bench.py's grid density (points per cell) for the BASELINE.json k values: first search radius just under two
+    cell widths; never below 1 point per cell."""
+    import math
+    import cuda_knearests_b200 as K
+    assert [K.fast_density(k) for k in (8, 20, 32, 50)] == [1.0, 1.0, 1.5, 2.1]
+    for k in (20, 32, 50, 100):
+        lam = k + 2.5 * math.sqrt(k) + 2.0
+        r0_cells = (3.0 * lam / (4.0 * math.pi * K.fast_density(k))) ** (1.0 / 3.0)
+        assert 1.9 < r0_cells < 2.0
