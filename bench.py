@@ -77,7 +77,7 @@ def measured_peak_gbs():
 
 
 class ClockSampler:
-    """Samples SM clock and throttle reasons DURING the timed region (NVML, 100 ms period)."""
+    """Samples SM clock and throttle reasons DURING the timed region (NVML, 20 ms period)."""
     REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
                0x4: "sw_power_cap", 0x80: "hw_power_brake_slowdown"}
 
@@ -104,7 +104,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(0.1)
+            self._stop.wait(0.02)
 
     def __enter__(self):
         if self.nv:
