@@ -384,7 +384,7 @@ __global__ void __launch_bounds__(QB) kn_query_fast_kernel(const __grid_constant
 // k <= count <= capacity  =>  the row is exact (the whole sphere was searched and holds >= k points);
 // anything else goes to the retry list of the general kernel.
 // NET keys are sorted per round, CAP candidates can be buffered per lane (32-bit positions):
-//   k <= 20 : NET 32, CAP 56      k <= 50 : NET 64, CAP 100   (the last kSelChunk slots are overrun room,
+//   k <= 20 : NET 32, CAP 56      k = 32 : NET 64, CAP 92      k = 50 : NET 64, CAP 100   (the last kSelChunk slots are overrun room,
 //   and the query itself takes one)
 #ifndef KN_SEL_CHUNK
 #define KN_SEL_CHUNK 4
@@ -719,7 +719,7 @@ cudaError_t launch(const QueryParams &P, bool fast, cudaStream_t st) {
     constexpr bool kHasSelect = K_T == 8 || K_T == 20 || K_T == 32 || K_T == 50;
     if (fast && kHasSelect && P.use_select) {
         if constexpr (kHasSelect) {
-            constexpr int NET = K_T <= 20 ? 32 : 64, CAP = K_T <= 20 ? 56 : 100;  // 56: the most that still lets 6 blocks share an SM (6 x 38 KB = 228 KB)
+            constexpr int NET = K_T <= 20 ? 32 : 64, CAP = K_T <= 20 ? 56 : K_T <= 32 ? 92 : 100;  // 56 and 92: the most that still lets 6 resp. 4 blocks share an SM (228 KB)
             const size_t smem = (sizeof(unsigned) * CAP + sizeof(int2) * kSpanSlots) * QB;
             e = cudaFuncSetAttribute(kn_query_select_kernel<K_T, QB, NET, CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      (int)smem);
