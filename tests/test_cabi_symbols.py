@@ -80,3 +80,15 @@ def test_bench_grid_density_rule():
         lam = k + 2.5 * math.sqrt(k) + 2.0
         r0_cells = (3.0 * lam / (4.0 * math.pi * K.fast_density(k))) ** (1.0 / 3.0)
         assert 1.9 < r0_cells < 2.0
+
+
+def test_product_never_touches_the_oracle():
+    """oracle/ is test infrastructure: nothing under cuda_knearests_b200/ may import, link or open it
+    (bench.py's CPU baseline legs, smoke() and tests/ are the only users)."""
+    import pathlib
+    import re
+    root = pathlib.Path(__file__).resolve().parents[1] / "cuda_knearests_b200"
+    for f in list(root.glob("*.py")) + list((root / "csrc").glob("*.cu")) + list((root / "csrc").glob("*.h")) + \
+            [root / "csrc" / "Makefile"]:
+        text = f.read_text()
+        assert not re.search(r"\boracle\b|_ref/|libkn_oracle|libref_", text), f"{f} refers to the oracle"
