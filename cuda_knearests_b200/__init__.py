@@ -25,7 +25,7 @@ MAX_K = 256
 
 # every symbol include/knearests_c.h declares (tests check that the library exports all of them)
 C_ABI_SYMBOLS = [
-    "knc_prepare", "knc_prepare_ex", "knc_solve", "knc_solve_to_host", "knc_free", "knc_get_points", "knc_get_permutation",
+    "knc_prepare", "knc_prepare_ex", "knc_solve", "knc_solve_to_host", "knc_free", "knc_trim", "knc_get_points", "knc_get_permutation",
     "knc_get_knearests", "knc_get_knearests_original", "knc_get_stats", "knc_get_info", "knc_get_timings",
     "knc_grid_dim", "knc_last_error", "knc_version", "knc_generate_uniform_device", "knc_scan_cells_noalloc",
     "knc_slab_route", "knc_get_knearests_global", "knc_set_index_offset", "knc_get_permutation_global",

@@ -53,22 +53,35 @@ bool verbose() {
         }                                                                                          \
     } while (0)
 
-// Stream-ordered allocations from the device's default pool, which we ask to keep freed memory: a
-// caller that prepares cloud after cloud (bench, services) pays the driver's page mapping once.
-cudaError_t dev_alloc(void **p, size_t bytes, cudaStream_t st) {
-    return cudaMallocAsync(p, bytes ? bytes : 1, st);
-}
+// Stream-ordered allocations from a PRIVATE memory pool per device, which keeps freed memory (release threshold
+// = never): a caller that prepares cloud after cloud (bench, services) pays the driver's page mapping once.  The
+// device's default pool -- which other libraries in the process share -- is left untouched; knc_trim() hands the
+// cached memory back to the driver.
+cudaMemPool_t g_pool[64] = {nullptr};
+std::mutex g_pool_lock;
 
-void keep_pool_memory(int device) {
-    static bool done[64] = {false};
-    if (device < 0 || device >= 64 || done[device]) return;
-    cudaMemPool_t pool;
-    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+cudaError_t device_pool(int device, cudaMemPool_t *out) {
+    if (device < 0 || device >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> hold(g_pool_lock);
+    if (!g_pool[device]) {
+        cudaMemPoolProps props;
+        memset(&props, 0, sizeof(props));
+        props.allocType = cudaMemAllocationTypePinned;
+        props.handleTypes = cudaMemHandleTypeNone;
+        props.location.type = cudaMemLocationTypeDevice;
+        props.location.id = device;
+        cudaMemPool_t pool;
+        cudaError_t e = cudaMemPoolCreate(&pool, &props);
+        if (e != cudaSuccess) return e;
         unsigned long long keep = ~0ull;
         cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        g_pool[device] = pool;
     }
-    done[device] = true;
+    *out = g_pool[device];
+    return cudaSuccess;
 }
+
+cudaError_t dev_alloc(void **p, size_t bytes, cudaStream_t st) { return kn_dev_alloc(p, bytes, st); }
 
 // Streams and events are recycled: creating and destroying them are kernel-mode driver calls that cost
 // a noticeable fraction of a millisecond each, more when several processes share the host (one per GPU).
@@ -121,6 +134,17 @@ void free_device_state(knc_problem *p) {
 
 }  // namespace
 
+// Allocation for every translation unit of the library: stream-ordered, from the library's own pool on the
+// current device.  Freed with cudaFreeAsync.
+cudaError_t kn_dev_alloc(void **p, size_t bytes, cudaStream_t st) {
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
+    cudaMemPool_t pool;
+    if (e == cudaSuccess) e = device_pool(device, &pool);
+    if (e != cudaSuccess) return e;
+    return cudaMallocFromPoolAsync(p, bytes ? bytes : 1, pool, st);
+}
+
 // Lets the other translation units of the library report through knc_last_error().
 int kn_set_error(int code, const char *fmt, ...) {
     va_list ap;
@@ -138,6 +162,18 @@ const char *knc_version(void) {
     static char v[96];
     snprintf(v, sizeof(v), "knearests_b200 %s sm_100a k_default=%d", KN_VERSION, DEFAULT_NB_PLANES);
     return v;
+}
+
+int knc_trim(void) {
+    int rc = KNC_OK, device = 0;
+    CU(cudaGetDevice(&device));
+    CU(cudaDeviceSynchronize());
+    {
+        std::lock_guard<std::mutex> hold(g_pool_lock);
+        if (device >= 0 && device < 64 && g_pool[device]) CU(cudaMemPoolTrimTo(g_pool[device], 0));
+    }
+out:
+    return rc;
 }
 
 int knc_grid_dim(int n, float density) {
@@ -185,7 +221,6 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     GridGeom g;
 
     CU(cudaGetDevice(&p->device));
-    keep_pool_memory(p->device);
     {
         StreamKit kit;
         CU(take_kit(p->device, &kit));

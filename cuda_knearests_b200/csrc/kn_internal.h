@@ -73,5 +73,6 @@ cudaError_t kn_launch_rows_dists(const float4 *d_points4, const unsigned int *d_
 
 // ---- api.cu ------------------------------------------------------------------------------------
 int kn_set_error(int code, const char *fmt, ...);  // records the message knc_last_error() returns
+cudaError_t kn_dev_alloc(void **p, size_t bytes, cudaStream_t st);  // stream-ordered, from the library's private pool
 
 #define KN_BIG_CELL 32  // cells with more points than this are ordered by a whole block, not a thread

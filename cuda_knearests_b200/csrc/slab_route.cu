@@ -173,14 +173,15 @@ kn_route_scatter_kernel(const float *__restrict__ xyz, int n, unsigned first_id,
 }
 
 // rows[r*k + j] = ids[perm[knn[r*k + j]]], query_ids[r] = ids[perm[query_begin + r]]
+// (the stored rows hold local sorted position + index_offset, knc_set_index_offset)
 __global__ void kn_rows_to_global_kernel(const unsigned *__restrict__ knn, const unsigned *__restrict__ perm,
                                          const unsigned *__restrict__ ids, int id_stride, int query_begin,
-                                         long long total, int k, unsigned *__restrict__ out_rows,
-                                         unsigned *__restrict__ out_query_ids) {
+                                         unsigned index_offset, long long total, int k,
+                                         unsigned *__restrict__ out_rows, unsigned *__restrict__ out_query_ids) {
     const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= total) return;
     const unsigned v = __ldg(knn + e);
-    out_rows[e] = v == KNC_EMPTY ? KNC_EMPTY : __ldg(ids + (size_t)id_stride * __ldg(perm + v));
+    out_rows[e] = v == KNC_EMPTY ? KNC_EMPTY : __ldg(ids + (size_t)id_stride * __ldg(perm + (v - index_offset)));
     const long long r = e / k;
     if (out_query_ids && e - r * k == 0)
         out_query_ids[r] = __ldg(ids + (size_t)id_stride * __ldg(perm + query_begin + r));
@@ -246,8 +247,8 @@ extern "C" int knc_route_begin(const float *d_xyz, int n, unsigned int first_id,
     cudaError_t e = cudaSuccess;
     if (n > 0) {
         cudaStream_t st = 0;
-        e = cudaMallocAsync((void **)&r->d_counts, sizeof(int) * (size_t)nranks * r->nblocks, st);
-        if (e == cudaSuccess) e = cudaMallocAsync((void **)&r->d_tot, sizeof(long long) * kMaxRanks, st);
+        e = kn_dev_alloc((void **)&r->d_counts, sizeof(int) * (size_t)nranks * r->nblocks, st);
+        if (e == cudaSuccess) e = kn_dev_alloc((void **)&r->d_tot, sizeof(long long) * kMaxRanks, st);
         if (e == cudaSuccess) {
             kn_route_count_kernel<<<r->nblocks, kRouteThreads, 0, st>>>(d_xyz, n, (float)grid_dim, grid_dim, r->pl, r->nblocks,
                                                                        r->d_counts);
@@ -317,7 +318,10 @@ extern "C" int knc_peer_alloc(size_t bytes, void **d_ptr, unsigned char *handle6
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     cudaError_t e = cudaMalloc(d_ptr, bytes);  // plain cudaMalloc: pool memory cannot be exported
     cudaIpcMemHandle_t h;
-    if (e == cudaSuccess) e = cudaIpcGetMemHandle(&h, *d_ptr);
+    if (e == cudaSuccess) {
+        e = cudaIpcGetMemHandle(&h, *d_ptr);
+        if (e != cudaSuccess) { cudaFree(*d_ptr); *d_ptr = nullptr; }  // not exportable: do not leak the buffer
+    }
     if (e != cudaSuccess) return kn_set_error(e == cudaErrorMemoryAllocation ? KNC_ERR_NOMEM : KNC_ERR_CUDA, "knc_peer_alloc: %s",
                                               cudaGetErrorString(e));
     memcpy(handle64, &h, 64);
@@ -351,8 +355,8 @@ extern "C" int knc_get_knearests_global(knc_problem *p, const unsigned int *d_id
     const long long total = (long long)p->query_count * p->k;
     if (total > 0) {
         kn_rows_to_global_kernel<<<(unsigned)((total + 255) / 256), 256, 0, p->stream>>>(
-            p->pub.d_knearests, p->pub.d_permutation, d_ids, id_stride, p->query_begin, total, p->k, d_out_rows,
-            d_out_query_ids);
+            p->pub.d_knearests, p->pub.d_permutation, d_ids, id_stride, p->query_begin, p->index_offset, total, p->k,
+            d_out_rows, d_out_query_ids);
         cudaError_t e = cudaGetLastError();
         if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
         if (e != cudaSuccess) return kn_set_error(KNC_ERR_CUDA, "knc_get_knearests_global: %s", cudaGetErrorString(e));

@@ -284,7 +284,8 @@ def solve_distributed(local_xyz, first_id: int, n_total: int, k: int, group=None
 
 
 # ------------------------------------------------------------------------------------------- bench
-def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_config, ClockSampler, measured_peak_gbs):
+def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_config, ClockSampler, measured_peak_gbs,
+                verify=None):
     """bench.py for N > 1: 100 M points cut into z-slabs, strong scaling.  A step is the whole multi-GPU
     hot path: route + NCCL all-to-all + kn_prepare (slab) + kn_solve (rows in global sorted positions) +
     this rank's slice of the global permutation."""
@@ -347,6 +348,21 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
     allstats = [torch.empty_like(stats) for _ in range(world)]
     dist.all_gather(allstats, stats)
 
+    # after the timed region: every rank has the caller's checker (bench.py: the CPU oracle) look at sampled rows of
+    # one more pass -- rows in global sorted positions, the id table (tags) and the cell pointers of its slab
+    checks = [None] * world
+    if verify is not None:
+        r = solve_distributed(pts, lo, n, k, density=args.density or 3.1, peers=peers)
+        mine = {"queries": 0, "mismatches": 0}
+        if r.handle is not None:
+            i = r.handle.info
+            cells = i.dimx * i.dimy * (i.z_end - i.z_begin)
+            mine = verify(torch, r.rows, torch.as_tensor(_DevView(r.handle.tags_ptr(), (i.n,)), device=dev),
+                          torch.as_tensor(_DevView(i.d_ptrs, (cells + 1,)), device=dev), i, r.base - i.query_begin,
+                          n, k, seed=rank)
+        r.free()
+        dist.all_gather_object(checks, mine)
+
     e2e = None
     if not args.no_e2e:
         host_in = torch.empty((hi - lo, 3), dtype=torch.float32, pin_memory=True)
@@ -405,6 +421,9 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
                 "cpu_baseline": None,
                 "device_ms": {"query_max_over_ranks": solve_ms,
                               "grid_build_max_over_ranks": max(float(s[1].item()) for s in allstats)},
+                "verify": None if verify is None else {
+                    "queries": sum(c["queries"] for c in checks), "mismatches": sum(c["mismatches"] for c in checks),
+                    "per_rank": checks},
                 "queries_per_rank": queries, "halo_attempts": infos[-1]["attempts"],
                 "phase_ms_rank0_instrumented": {kk: round(v, 3) for kk, v in phase_ms.items()}}
         print(json.dumps(line), flush=True)

@@ -121,6 +121,13 @@ int knc_solve_to_host(knc_problem *p, unsigned int *out_knn, int chunks);
 /* Replaces kn_free (knearests.h:23, knearests.cu:396-408).  NULL is accepted. */
 int knc_free(knc_problem *p);
 
+/* Device memory the library frees is kept in a PRIVATE stream-ordered pool per device (cudaMemPoolCreate; the
+ * device's default pool, which other libraries of the process share, is never touched), so that preparing
+ * cloud after cloud does not pay the driver's page mapping again (the reference cudaMallocs and cudaFrees
+ * every buffer per problem, knearests.cu:205-231,396-408).  After knc_free the memory therefore still counts
+ * as used for everyone else: knc_trim gives all of it back to the driver (current device; blocking). */
+int knc_trim(void);
+
 /* Replace kn_get_points / kn_get_permutation / kn_get_knearests (knearests.h:25-27,
  * knearests.cu:410-438), writing into CALLER-provided host buffers instead of malloc()ing:
  *   out_xyz   3*n floats            out_perm  n unsigned          out_knn  query_count*k unsigned  */
@@ -241,7 +248,8 @@ int knc_get_knearests_global(knc_problem *p, const unsigned int *d_ids, int id_s
  * loads the library until exit, which is why at most KNC_NOALLOC_MAX_CELLS cells are accepted (a
  * 256^3 grid, ~52 M points at the default density); larger sizes return KNC_ERR_INVALID.
  * The first call on a device resolves the scratch address: make it at start-up, before any stream
- * capture.  All calls on a device share the scratch; each clears what it uses first, so calls whose GPU
+ * capture.  The address is remembered per device for the life of the process; it does not survive a
+ * cudaDeviceReset (do not reset a device this entry point has been used on).  All calls on a device share the scratch; each clears what it uses first, so calls whose GPU
  * work could overlap (other streams, other threads) race and must be serialised by the caller.
  * Blocking: returns when `stream` has drained. */
 #define KNC_NOALLOC_MAX_CELLS 16777216LL

@@ -219,6 +219,9 @@ class RefKdTree:
                                           C.c_void_p, C.c_int]
         self.L.ref_kdtree_knn.restype = C.c_int
         self.L.ref_kdtree_max_threads.restype = C.c_int
+        self.L.ref_kdtree_knn_passes.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, C.c_int, _i32p, C.c_void_p,
+                                                 C.c_int, C.c_int]
+        self.L.ref_kdtree_knn_passes.restype = C.c_int
 
     def max_threads(self) -> int:
         return int(self.L.ref_kdtree_max_threads())
@@ -235,6 +238,14 @@ class RefKdTree:
                                      C.addressof(times), threads)
         info = {"build_s": times[0], "query_s": times[1], "threads": used}
         return (out, d2, info) if with_d2 else (out, info)
+
+    def knn_passes(self, xyz: np.ndarray, K: int, q0: int, q1: int, threads: int, passes: int):
+        """One tree build, `passes` query passes over the points [q0, q1): (rows of the last pass, info)."""
+        xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
+        out = np.empty((q1 - q0, K), np.int32)
+        times = (C.c_double * (1 + passes))()
+        used = self.L.ref_kdtree_knn_passes(xyz, xyz.shape[0], q0, q1, K, out, C.addressof(times), threads, passes)
+        return out, {"build_s": times[0], "query_s": [times[1 + i] for i in range(passes)], "threads": used}
 
 
 def ref_load_xyz(path: str) -> np.ndarray:

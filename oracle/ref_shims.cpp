@@ -54,6 +54,35 @@ int ref_kdtree_knn(const float *xyz, int n, int q0, int q1, int K, int *out_idx,
     return used;
 }
 
+// Same, with the query pass repeated `passes` times over the ONE tree (the tree build of a 100 M-point cloud takes
+// minutes, a query pass over a sample seconds): times[0] = build seconds, times[1 + i] = seconds of pass i.
+// Only the last pass's rows are kept.  Used by bench.py's CPU arm for a warm-up pass and timed passes.
+int ref_kdtree_knn_passes(const float *xyz, int n, int q0, int q1, int K, int *out_idx, double *times,
+                          int num_threads, int passes) {
+    using clk = std::chrono::steady_clock;
+    auto t0 = clk::now();
+    KdTree KD(3);
+    KD.set_points(n, xyz);
+    times[0] = std::chrono::duration<double>(clk::now() - t0).count();
+    int used = 1;
+#ifdef _OPENMP
+    if (num_threads > 0) omp_set_num_threads(num_threads);
+    used = omp_get_max_threads();
+#endif
+    for (int pass = 0; pass < passes; ++pass) {
+        auto t1 = clk::now();
+#pragma omp parallel for schedule(dynamic, 256)
+        for (int v = q0; v < q1; ++v) {  // test_knearests.cu:203-212
+            std::vector<int> neigh(K + 1);
+            std::vector<float> sq(K + 1);
+            KD.get_nearest_neighbors(K + 1, v, neigh.data(), sq.data());
+            for (int j = 0; j < K; ++j) out_idx[(size_t)(v - q0) * K + j] = neigh[j + 1];
+        }
+        times[1 + pass] = std::chrono::duration<double>(clk::now() - t1).count();
+    }
+    return used;
+}
+
 int ref_kdtree_max_threads() {
 #ifdef _OPENMP
     return omp_get_max_threads();

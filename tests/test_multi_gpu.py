@@ -68,6 +68,11 @@ def test_emulated_ranks_reproduce_single_gpu_rows(kn, oracle, world, k, n):
             kn._check(kn.lib().knc_set_index_offset(p._h, base - p.info.query_begin))
             p.solve()
             got_rows.append(p.get_knearests())
+            # the same call AFTER the offset (rows now hold global positions): must subtract it again
+            rows2 = torch.full((nq, k), -1, dtype=torch.int32, device="cuda")
+            torch.cuda.synchronize()
+            kn._check(kn.lib().knc_get_knearests_global(p._h, ids_ptr, 4, C.c_void_p(rows2.data_ptr()), None))
+            assert torch.equal(rows2, rows)
             perm = torch.empty((nq,), dtype=torch.int32, device="cuda")
             torch.cuda.synchronize()
             kn._check(kn.lib().knc_get_permutation_global(p._h, ids_ptr, 4, C.c_void_p(perm.data_ptr())))
