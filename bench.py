@@ -44,7 +44,7 @@ sys.path.insert(0, str(ROOT))
 SEED = 20171004
 METRIC = "kNN queries/sec"
 UNIT = "queries/s"
-KERNELS_PER_STEP = 11  # z-band split (3), count, scan, scatter, order, order_big, gather, query (select), query (retry)
+KERNELS_PER_STEP = 12  # z-band split (3), count, scan, scatter, order, order_big, gather, query (tile, select for handed-over blocks, retry)
 
 
 def parse():
@@ -63,16 +63,12 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--density", type=float, default=0.0,
-                    help="points per grid cell handed to knc_prepare_ex (library default: the reference's 3.1); "
-                         "0 = cuda_knearests_b200.fast_density(k): 1.0 at k=20, ~14 %% faster on B200 than 3.1, "
-                         "profiles/r1_notes.md")
-    ap.add_argument("--algorithm", type=int, default=0, help="knc_options.algorithm (0 auto, 1 general, 2 insertion kernel)")
+                    help="> 0: a cubic grid with this many points per cell (3.1 = the reference's grid, "
+                         "knearests.cu:249); 0 = the library's default grid (knc_fast_dims), what kn_prepare uses")
+    ap.add_argument("--algorithm", type=int, default=0,
+                    help="knc_options.algorithm (0 auto, 1 general kernel, 2 insertion kernel, 4 without the tile kernel)")
     ap.add_argument("--no-ref-gpu", action="store_true", help="skip timing the reference's own knearests.cu on this GPU")
-    args = ap.parse_args()
-    if args.density <= 0:
-        from cuda_knearests_b200 import fast_density
-        args.density = fast_density(args.k)
-    return args
+    return ap.parse_args()
 
 
 def measured_peak_gbs():
@@ -244,8 +240,10 @@ def verify_against_oracle(torch, rows, idtable, ptrs, info, index_offset: int, n
 def workload_config(args):
     c = {"workload": f"synthetic uniform {args.n} points in [0,1000)^3 (splitmix64 counter generator, seed {SEED}), "
                      f"k={args.k}: kn_prepare + kn_solve", "n_points": args.n, "k": args.k,
-         "grid_density": args.density,
-         "l2_policy": "inputs larger than L2 (points 12 B x n, rows 4k B x n >> 126 MB); no flush needed"}
+         "grid": (f"cube, {args.density} points per cell" if args.density > 0 else
+                  "library default (knc_fast_dims: y/z cells as wide as the first search radius, ~1 point per cell)"),
+         "l2_policy": "inputs larger than L2 (points 12 B x n, rows 4k B x n >> 126 MB); no flush needed",
+         "parallelism": "single GPU" if args.gpus <= 1 else f"z-slabs x{args.gpus}"}
     return c
 
 
@@ -291,6 +289,7 @@ def main_ours(args, rank: int, world: int, local_rank: int):
     value = n / (wall / args.steps)
     solve_ms = float(np.mean([t["solve_ms"] for t in timings]))
     build_ms = float(np.mean([t["build_ms"] for t in timings]))
+    grid_dims = list(K.fast_dims(n, k)) if args.density <= 0 else [K.grid_dim(n, args.density)] * 3
 
     peak, peak_kind = measured_peak_gbs()
     algo_bytes = (12 + 4 * k) * n
@@ -303,7 +302,7 @@ def main_ours(args, rank: int, world: int, local_rank: int):
         except Exception:
             traffic = None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": "kn_query_select_kernel (+ retry kernel)", "kernel_ms": solve_ms,
+                "traffic": traffic, "kernel": "kn_query_tile_kernel (+ select kernel for handed-over blocks + retry kernel)", "kernel_ms": solve_ms,
                 "algorithmic_bytes": algo_bytes, "peak_kind": f"{peak_kind} copy bandwidth (burst)"}
 
     # ---- after the timed region: sampled rows of one more (untimed) pass, checked by the CPU oracle ------------
@@ -380,7 +379,8 @@ def main_ours(args, rank: int, world: int, local_rank: int):
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args),
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args), "grid_dims": grid_dims,
             "clocks": clk.summary(), "e2e": e2e, "gpu_launches": KERNELS_PER_STEP * args.steps,
             "roofline": roofline, "cpu_baseline": cpu_baseline,
             "device_ms": {"grid_build": build_ms, "query": solve_ms},

@@ -27,7 +27,7 @@ MAX_K = 256
 C_ABI_SYMBOLS = [
     "knc_prepare", "knc_prepare_ex", "knc_solve", "knc_solve_to_host", "knc_free", "knc_trim", "knc_get_points", "knc_get_permutation",
     "knc_get_knearests", "knc_get_knearests_original", "knc_get_stats", "knc_get_info", "knc_get_timings",
-    "knc_grid_dim", "knc_last_error", "knc_version", "knc_generate_uniform_device", "knc_scan_cells_noalloc",
+    "knc_grid_dim", "knc_fast_dims", "knc_last_error", "knc_version", "knc_generate_uniform_device", "knc_scan_cells_noalloc",
     "knc_slab_route", "knc_get_knearests_global", "knc_set_index_offset", "knc_get_permutation_global",
     "knc_get_dists", "knc_query_points", "knc_get_tags",
     "knc_route_begin", "knc_route_scatter", "knc_route_end",
@@ -42,11 +42,12 @@ CXX_ABI_SYMBOLS = [
 
 
 def fast_density(k: int) -> float:
-    """Points per grid cell at which the query kernels run fastest on B200 for uniform clouds (measured at 100 M
-    points, profiles/r1_notes.md): the first search radius -- a sphere expected to hold k + 2.5 sqrt(k) + 2 points,
-    knn_query.cu -- should stay just under 2 cell widths, so that rows three cells away never enter the row table.
-    1.0 / 1.0 / 1.5 / 2.1 for k = 8 / 20 / 32 / 50.  The library default remains the reference's 3.1
-    (knearests.cu:249); the choice changes speed, never results."""
+    """Points per cell at which the query kernels run fastest on a CUBIC grid on B200 for uniform clouds (measured at
+    100 M points, profiles/r1_notes.md): the first search radius -- a sphere expected to hold k + 2.5 sqrt(k) + 2
+    points, knn_query.cu -- should stay just under 2 cell widths, so that rows three cells away never enter the row
+    table.  1.0 / 1.0 / 1.5 / 2.1 for k = 8 / 20 / 32 / 50.  (Round 1's bench grid; the library default is now the
+    non-cubic grid of fast_dims / knc_fast_dims, and density = 3.1 gives the reference's, knearests.cu:249.)  The
+    choice changes speed, never results."""
     import math
     lam = k + 2.5 * math.sqrt(k) + 2.0
     cells_in_radius_2 = 4.0 / 3.0 * math.pi * 8.0
@@ -63,7 +64,8 @@ class Options(C.Structure):  # knc_options
     _fields_ = [("struct_size", C.c_size_t), ("k", C.c_int), ("density", C.c_float),
                 ("points_on_device", C.c_int), ("grid_dim", C.c_int), ("z_begin", C.c_int),
                 ("z_end", C.c_int), ("own_z_begin", C.c_int), ("own_z_end", C.c_int),
-                ("search_scale", C.c_float), ("algorithm", C.c_int), ("point_stride", C.c_int)]
+                ("search_scale", C.c_float), ("algorithm", C.c_int), ("point_stride", C.c_int),
+                ("grid_dims", C.c_int * 3)]
 
 
 class Info(C.Structure):  # knc_info
@@ -116,6 +118,7 @@ def lib() -> C.CDLL:
         L.knc_get_info.argtypes = [vp, C.POINTER(Info)]
         L.knc_get_timings.argtypes = [vp, C.POINTER(Timings)]
         L.knc_grid_dim.argtypes = [C.c_int, C.c_float]
+        L.knc_fast_dims.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_int)]
         L.knc_generate_uniform_device.argtypes = [vp, C.c_longlong, C.c_longlong, C.c_uint64]
         L.knc_scan_cells_noalloc.argtypes = [vp, C.c_longlong, vp, vp]
         L.knc_slab_route.argtypes = [vp, C.c_int, C.c_uint, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, vp,
@@ -147,6 +150,14 @@ def grid_dim(n: int, density: float = 3.1) -> int:
     return int(lib().knc_grid_dim(int(n), float(density)))
 
 
+def fast_dims(n: int, k: int = 0) -> tuple:
+    """(dimx, dimy, dimz) of the grid the library chooses by default (knc_fast_dims): y/z cells a little wider than
+    the first search radius, narrow x cells, about one point per cell."""
+    d = (C.c_int * 3)()
+    _check(lib().knc_fast_dims(int(n), int(k), d))
+    return int(d[0]), int(d[1]), int(d[2])
+
+
 def version() -> str:
     return lib().knc_version().decode()
 
@@ -160,13 +171,15 @@ class KnProblem:
     """
 
     def __init__(self, points, k: int = 0, density: float = 0.0, grid_dim: int = 0, slab=None,
-                 search_scale: float = 0.0, algorithm: int = 0):
+                 search_scale: float = 0.0, algorithm: int = 0, grid_dims=None):
         self._h = C.c_void_p()
         opt = Options()
         opt.struct_size = C.sizeof(Options)
         opt.k = int(k)
         opt.density = float(density)
         opt.grid_dim = int(grid_dim)
+        if grid_dims is not None:
+            opt.grid_dims[0], opt.grid_dims[1], opt.grid_dims[2] = (int(v) for v in grid_dims)
         opt.search_scale = float(search_scale)
         opt.algorithm = int(algorithm)
         if slab is not None:

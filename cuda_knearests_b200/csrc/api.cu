@@ -183,6 +183,29 @@ int knc_grid_dim(int n, float density) {
     return sz < 1 ? 1 : sz;
 }
 
+// Radius of the sphere expected to hold k + 2.5 sqrt(k) + 2 points at `rho` points per unit volume: the first search
+// radius of every query kernel (knn_query.cu).
+static double radius_for(int k, double rho) {
+    const double lambda = k + 2.5 * sqrt((double)k) + 2.0;
+    return cbrt(3.0 * lambda / (4.0 * M_PI * rho));
+}
+
+int knc_fast_dims(int n, int k, int *dims) {
+    if (!dims || n < 1) return fail(KNC_ERR_INVALID, "knc_fast_dims: bad argument");
+    if (k <= 0) k = default_k();
+    // y and z: cells 2 % wider than the first search radius, so that a query's sphere never reaches past the 3 x 3
+    // x-rows of cells around its own (what the tile kernel stages in shared memory);  x: as many cells as points
+    const double r0 = radius_for(k, (double)n / 1e9);
+    int dyz = (int)floor(1000.0 / (1.02 * r0));
+    if (dyz < 1) dyz = 1;
+    if (dyz > 1024) dyz = 1024;
+    long long dx = llround((double)n / ((double)dyz * dyz));
+    if (dx < 1) dx = 1;
+    if (dx > 1048576) dx = 1048576;
+    dims[0] = (int)dx; dims[1] = dyz; dims[2] = dyz;
+    return KNC_OK;
+}
+
 int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem **out) {
     int rc = KNC_OK;
     knc_options o;
@@ -194,26 +217,36 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     if (n < 1) return fail(KNC_ERR_INVALID, "knc_prepare: n = %d, need at least 1 point", n);
     const int k = o.k > 0 ? o.k : default_k();
     if (k > KNC_MAX_K) return fail(KNC_ERR_INVALID, "knc_prepare: k = %d exceeds KNC_MAX_K = %d", k, KNC_MAX_K);
-    // points per cell: the caller's choice, else the environment (drop-in callers cannot pass options), else the
-    // reference's 3.1 (knearests.cu:249)
-    float density = 3.1f;
+    // The grid, in order of precedence: explicit resolutions (grid_dims, or the cube grid_dim), a cube from a number
+    // of points per cell (the caller's `density`, else the environment's KN_GRID_DENSITY -- drop-in callers cannot
+    // pass options; 3.1 gives the reference's grid, knearests.cu:249), else the grid the B200 kernels are built for
+    // (knc_fast_dims: as fast as any cube and it changes no result, only dimx/dimy/dimz and the cell order).
+    float density = 0.f;
     if (o.density > 0.f) density = o.density;
     else if (const char *e = getenv("KN_GRID_DENSITY")) { if (atof(e) > 0.) density = (float)atof(e); }
     const int stride = o.point_stride > 0 ? o.point_stride : 3;
     if (stride != 3 && stride != 4) return fail(KNC_ERR_INVALID, "knc_prepare: point_stride = %d, supported 3 or 4", stride);
-    const int D = o.grid_dim > 0 ? o.grid_dim : knc_grid_dim(n, density);
-    if ((long long)D * D * D > 2000000000ll) return fail(KNC_ERR_INVALID, "knc_prepare: grid %d^3 too large", D);
+    int dims[3];
+    const bool dims_given = o.grid_dims[0] > 0 && o.grid_dims[1] > 0 && o.grid_dims[2] > 0;
+    if (dims_given) { dims[0] = o.grid_dims[0]; dims[1] = o.grid_dims[1]; dims[2] = o.grid_dims[2]; }
+    else if (o.grid_dim > 0) dims[0] = dims[1] = dims[2] = o.grid_dim;
+    else if (density > 0.f) dims[0] = dims[1] = dims[2] = knc_grid_dim(n, density);
+    else knc_fast_dims(n, k, dims);
+    if ((long long)dims[0] * dims[1] * dims[2] > 2000000000ll)
+        return fail(KNC_ERR_INVALID, "knc_prepare: grid %d x %d x %d too large", dims[0], dims[1], dims[2]);
+    const int D = dims[2];  // planes: slabs cut the z axis
     int zb = 0, ze = D, ozb = 0, oze = D;
     if (o.z_begin || o.z_end || o.own_z_begin || o.own_z_end) {
         zb = o.z_begin; ze = o.z_end; ozb = o.own_z_begin; oze = o.own_z_end;
-        if (o.grid_dim <= 0 || zb < 0 || ze > D || zb >= ze || ozb < zb || oze > ze || ozb > oze)
-            return fail(KNC_ERR_INVALID, "knc_prepare: bad slab planes [%d,%d) own [%d,%d) of D=%d (grid_dim must be set)",
+        if ((o.grid_dim <= 0 && !dims_given) || zb < 0 || ze > D || zb >= ze || ozb < zb || oze > ze || ozb > oze)
+            return fail(KNC_ERR_INVALID, "knc_prepare: bad slab planes [%d,%d) own [%d,%d) of %d (grid_dim / grid_dims must be set)",
                         zb, ze, ozb, oze, D);
     }
 
     knc_problem *p = (knc_problem *)calloc(1, sizeof(knc_problem));
     if (!p) return fail(KNC_ERR_NOMEM, "knc_prepare: out of host memory");
-    const long long cells = (long long)D * D * (ze - zb);
+    const long long cells = (long long)dims[0] * dims[1] * (ze - zb);
+    const long long plane = (long long)dims[0] * dims[1];
     float *d_in = NULL;
     BuildScratch s;
     memset(&s, 0, sizeof(s));
@@ -231,9 +264,9 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     p->k = k; p->density = density; p->search_scale = o.search_scale > 0.f ? o.search_scale : 1.f;
     p->algorithm = o.algorithm;
     p->z_begin = zb; p->z_end = ze; p->own_z_begin = ozb; p->own_z_end = oze;
-    p->dim_global = D; p->cells = cells;
+    p->dims[0] = dims[0]; p->dims[1] = dims[1]; p->dims[2] = dims[2]; p->cells = cells;
     p->pub.allocated_points = n;
-    p->pub.dimx = D; p->pub.dimy = D; p->pub.dimz = D;
+    p->pub.dimx = dims[0]; p->pub.dimy = dims[1]; p->pub.dimz = dims[2];
     p->pub.num_cell_offsets = 0;
 
     // persistent buffers (knearests.cu:313-335, without the `bufsize +=` over-allocation)
@@ -241,7 +274,7 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     CU(dev_alloc((void **)&p->pub.d_ptrs, sizeof(int) * (size_t)(cells + 1), st));
     CU(dev_alloc((void **)&p->pub.d_globcounter, sizeof(int), st));
     CU(dev_alloc((void **)&p->pub.d_cell_max, sizeof(float), st));
-    CU(dev_alloc((void **)&p->d_diag, sizeof(unsigned) * 4, st));
+    CU(dev_alloc((void **)&p->d_diag, sizeof(unsigned) * KN_DIAG_WORDS, st));
     CU(dev_alloc((void **)&p->pub.d_permutation, sizeof(unsigned) * (size_t)n, st));
     CU(dev_alloc((void **)&p->pub.d_stored_points, sizeof(float) * 3 * (size_t)n, st));
     CU(dev_alloc((void **)&p->d_points4, sizeof(float4) * (size_t)n, st));
@@ -266,7 +299,7 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
         CU(dev_alloc((void **)&d_in, sizeof(float) * stride * (size_t)n, st));
         CU(cudaMemcpyAsync(d_in, xyz, sizeof(float) * stride * (size_t)n, cudaMemcpyHostToDevice, st));
     }
-    g.D = D; g.zb = zb; g.ze = ze; g.Df = (float)D; g.w = 1000.f / (float)D; g.invw = (float)D / 1000.f;
+    g = kn_make_geom(dims, zb, ze);
     CU(cudaEventRecord(p->ev[1], st));
     CU(kn_launch_build(d_in, stride, n, g, cells, p->pub.d_counters, p->pub.d_ptrs, p->pub.d_globcounter,
                        p->pub.d_permutation, (float *)p->pub.d_stored_points, p->d_points4, p->d_tags, s, st));
@@ -275,9 +308,9 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     {   // the queries are the points of the owned planes: one contiguous run of sorted positions
         int range[2] = {0, n};
         if (ozb != zb || oze != ze) {
-            CU(cudaMemcpyAsync(&range[0], p->pub.d_ptrs + (size_t)(ozb - zb) * D * D, sizeof(int),
+            CU(cudaMemcpyAsync(&range[0], p->pub.d_ptrs + (size_t)(ozb - zb) * plane, sizeof(int),
                                cudaMemcpyDeviceToHost, st));
-            CU(cudaMemcpyAsync(&range[1], p->pub.d_ptrs + (size_t)(oze - zb) * D * D, sizeof(int),
+            CU(cudaMemcpyAsync(&range[1], p->pub.d_ptrs + (size_t)(oze - zb) * plane, sizeof(int),
                                cudaMemcpyDeviceToHost, st));
         }
         CU(cudaStreamSynchronize(st));
@@ -289,7 +322,7 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     CU(cudaEventElapsedTime(&p->t.build_ms, p->ev[1], p->ev[2]));
     if (verbose())
         fprintf(stderr, "kn_firstbuild: %g msec (n=%d, grid %dx%dx%d planes [%d,%d), k=%d, h2d %g msec)\n",
-                p->t.build_ms, n, D, D, D, zb, ze, k, p->t.h2d_ms);
+                p->t.build_ms, n, dims[0], dims[1], dims[2], zb, ze, k, p->t.h2d_ms);
 out:
     if (!o.points_on_device && d_in) cudaFreeAsync(d_in, st);
     {
@@ -314,21 +347,21 @@ int knc_prepare(const float *xyz, int n, int k, knc_problem **out) {
     return knc_prepare_ex(xyz, n, &o, out);
 }
 
+static double first_radius(const knc_problem *p) {
+    const double volume = 1000.0 * 1000.0 * (1000.0 * (p->z_end - p->z_begin) / p->dims[2]);
+    return radius_for(p->k, (double)p->pub.allocated_points / volume) * p->search_scale;
+}
+
 // The query, optionally streamed to the host: the query range is cut into `chunks` pieces; the rows of
 // piece c travel device->host on a second stream while piece c+1 is being computed.
 static int solve_impl(knc_problem *p, unsigned int *out_knn_host, int chunks, const char *who) {
     int rc = KNC_OK;
     if (!p) return fail(KNC_ERR_INVALID, "%s: NULL handle", who);
     cudaStream_t st = p->stream;
-    GridGeom g;
-    const int D = p->dim_global;
-    g.D = D; g.zb = p->z_begin; g.ze = p->z_end; g.Df = (float)D; g.w = 1000.f / (float)D; g.invw = (float)D / 1000.f;
+    const GridGeom g = kn_make_geom(p->dims, p->z_begin, p->z_end);
     // first-guess radius: sphere expected to hold k + 2.5 sqrt(k) + 2 points at the cloud's mean density
-    const double volume = 1000.0 * 1000.0 * (1000.0 * (p->z_end - p->z_begin) / D);
-    const double rho = (double)p->pub.allocated_points / volume;
-    const double lambda = p->k + 2.5 * sqrt((double)p->k) + 2.0;
-    const double r0 = cbrt(3.0 * lambda / (4.0 * M_PI * rho)) * p->search_scale;
-    unsigned diag[4] = {0, 0, 0, 0};
+    const double r0 = first_radius(p);
+    unsigned diag[KN_DIAG_WORDS] = {0};
     int *d_retry = NULL;  // scratch of the solve: queries the fast kernel hands to the general kernel
     const int force_general = p->algorithm;  // 0 auto, 1 general kernel only, 2 insertion kernel for every k
     if (chunks < 1 || !out_knn_host) chunks = 1;
@@ -336,15 +369,15 @@ static int solve_impl(knc_problem *p, unsigned int *out_knn_host, int chunks, co
     const int per = (p->query_count + chunks - 1) / chunks;
     cudaEvent_t done[64];
     int made = 0;
-    CU(dev_alloc((void **)&d_retry, sizeof(int) * (size_t)(per > 0 ? per : 1), st));
+    CU(dev_alloc((void **)&d_retry, sizeof(int) * kn_retry_ints(per), st));
     if (out_knn_host && !p->copy_stream) CU(cudaStreamCreateWithFlags(&p->copy_stream, cudaStreamNonBlocking));
-    CU(cudaMemsetAsync(p->d_diag, 0, sizeof(unsigned) * 4, st));
+    CU(cudaMemsetAsync(p->d_diag, 0, sizeof(unsigned) * KN_DIAG_WORDS, st));
     CU(cudaEventRecord(p->ev[2], st));
     for (int c = 0; c < chunks; ++c) {
         const int q0 = c * per, qn = (p->query_count - q0) < per ? (p->query_count - q0) : per;
         if (qn <= 0) break;
         unsigned int *rows = p->pub.d_knearests + (size_t)q0 * p->k;
-        if (c) CU(cudaMemsetAsync(p->d_diag + 3, 0, sizeof(unsigned), st));  // the retry list starts empty
+        if (c) CU(cudaMemsetAsync(p->d_diag + 3, 0, sizeof(unsigned) * 2, st));  // the retry and block lists start empty
         CU(kn_launch_query(p->d_points4, p->pub.d_ptrs, g, p->pub.allocated_points, p->k, p->query_begin + q0, qn,
                            (float)(r0 * r0), rows, p->d_diag, d_retry, force_general, p->index_offset, NULL, st));
         if (out_knn_host) {
@@ -368,7 +401,7 @@ static int solve_impl(knc_problem *p, unsigned int *out_knn_host, int chunks, co
     if (verbose()) {
         fprintf(stderr, "kn_solve: %g msec\n", p->t.solve_ms);
         fprintf(stderr, "Max search radius: %g cells (first guess %g cells, %u of %d queries restarted)\n",
-                sqrt((double)p->t.max_radius2) / g.w, r0 / g.w, diag[0], p->query_count);
+                sqrt((double)p->t.max_radius2) / g.wy, r0 / g.wy, diag[0], p->query_count);
     }
     if (diag[2])
         rc = fail(KNC_ERR_HALO, "%s: %u queries reach beyond the halo planes [%d,%d) of this slab", who, diag[2],
@@ -386,12 +419,6 @@ int knc_solve_to_host(knc_problem *p, unsigned int *out_knn, int chunks) {
     return solve_impl(p, out_knn, chunks > 0 ? chunks : 8, "knc_solve_to_host");
 }
 
-static double first_radius(const knc_problem *p) {
-    const double volume = 1000.0 * 1000.0 * (1000.0 * (p->z_end - p->z_begin) / p->dim_global);
-    const double rho = (double)p->pub.allocated_points / volume;
-    const double lambda = p->k + 2.5 * sqrt((double)p->k) + 2.0;
-    return cbrt(3.0 * lambda / (4.0 * M_PI * rho)) * p->search_scale;
-}
 
 int knc_get_dists(knc_problem *p, float *out_d2) {
     int rc = KNC_OK;
@@ -419,16 +446,14 @@ int knc_query_points(knc_problem *p, const float *xyz, int m, unsigned int *out_
     if (!p || !xyz || !out_knn || m < 1) return fail(KNC_ERR_INVALID, "knc_query_points: bad argument");
     {
         cudaStream_t st = p->stream;
-        GridGeom g;
-        const int D = p->dim_global;
-        g.D = D; g.zb = p->z_begin; g.ze = p->z_end; g.Df = (float)D; g.w = 1000.f / (float)D; g.invw = (float)D / 1000.f;
+        const GridGeom g = kn_make_geom(p->dims, p->z_begin, p->z_end);
         const double r0 = first_radius(p);
         const size_t rows_bytes = sizeof(unsigned) * (size_t)m * p->k;
         CU(dev_alloc((void **)&d_q, sizeof(float) * 3 * (size_t)m, st));
         CU(dev_alloc((void **)&d_rows, rows_bytes, st));
-        CU(dev_alloc((void **)&d_diag, sizeof(unsigned) * 4, st));
+        CU(dev_alloc((void **)&d_diag, sizeof(unsigned) * KN_DIAG_WORDS, st));
         CU(cudaMemcpyAsync(d_q, xyz, sizeof(float) * 3 * (size_t)m, cudaMemcpyHostToDevice, st));
-        CU(cudaMemsetAsync(d_diag, 0, sizeof(unsigned) * 4, st));
+        CU(cudaMemsetAsync(d_diag, 0, sizeof(unsigned) * KN_DIAG_WORDS, st));
         CU(kn_launch_query(p->d_points4, p->pub.d_ptrs, g, p->pub.allocated_points, p->k, 0, m, (float)(r0 * r0), d_rows,
                            d_diag, NULL, 1, p->index_offset, d_q, st));
         CU(cudaMemcpyAsync(out_knn, d_rows, rows_bytes, cudaMemcpyDeviceToHost, st));

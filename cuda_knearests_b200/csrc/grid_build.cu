@@ -14,7 +14,8 @@
 //              sorts each cell's few entries by original index => the whole layout is the stable
 //              counting sort, bit-identical from run to run (the reference's is not).
 //  * the sorted points are written twice: float3 (the API's d_stored_points) and float4
-//              (x,y,z,bits(original index)) -- 16-byte records the query kernel loads with one LDG.128.
+//              (x,y,z,bits(own sorted position)) -- 16-byte records the query kernels load with one 128-bit
+//              load or copy into shared memory in bulk; the 4th word lets a staged copy name its source.
 //
 // HBM traffic per point (algorithmic): read 12 (count) + write 8 (cell id, rank) + read 8 / write 4
 // (scatter) + read 4+12 / write 12+16 (gather) + 8 per cell for the scan ~= 79 B/point.
@@ -72,10 +73,10 @@ kn_count_kernel(const float *__restrict__ xyz, int stride, int n, GridGeom g, in
     const bool valid = tid < here;
     int cell = -1 - (tid & 31);  // invalid lanes: unique keys, never grouped
     if (valid) {
-        int i = axis_cell(tile[3 * tid], g.Df, 0, g.D - 1);
-        int j = axis_cell(tile[3 * tid + 1], g.Df, 0, g.D - 1);
-        int k = axis_cell(tile[3 * tid + 2], g.Df, g.zb, g.ze - 1) - g.zb;
-        cell = i + (j + k * g.D) * g.D;  // z-major, knearests.cu:29
+        int i = axis_cell(tile[3 * tid], g.Dfx, 0, g.Dx - 1);
+        int j = axis_cell(tile[3 * tid + 1], g.Dfy, 0, g.Dy - 1);
+        int k = axis_cell(tile[3 * tid + 2], g.Dfz, g.zb, g.ze - 1) - g.zb;
+        cell = i + (j + k * g.Dy) * g.Dx;  // z-major, knearests.cu:29
     }
     // Warp-aggregated atomic: lanes in the same cell elect a leader that adds the group size once.
     // match.any costs one round per distinct value, so it is only used when the warp looks coherent
@@ -300,7 +301,7 @@ constexpr int kBinTile = kBinThreads * kBinItems;
 constexpr int kBinGroups = kBinItems * (kBinThreads / 32);  // warp-sized runs of consecutive points in a tile
 
 __device__ __forceinline__ int bin_of_z(float z, const GridGeom &g, int planes_per_bin) {
-    return (axis_cell(z, g.Df, g.zb, g.ze - 1) - g.zb) / planes_per_bin;
+    return (axis_cell(z, g.Dfz, g.zb, g.ze - 1) - g.zb) / planes_per_bin;
 }
 
 // lanes of the warp holding the same band (6 votes; only meaningful on valid lanes)
@@ -493,7 +494,7 @@ kn_gather_kernel(const float *__restrict__ xyz, int stride, int n, unsigned int 
             i = __float_as_uint(v.w);
             permutation[s] = i;
         }
-        points4[s] = make_float4(x, y, z, __uint_as_float(i));
+        points4[s] = make_float4(x, y, z, __uint_as_float((unsigned)s));
         tile[3 * tid] = x; tile[3 * tid + 1] = y; tile[3 * tid + 2] = z;
     }
     __syncthreads();

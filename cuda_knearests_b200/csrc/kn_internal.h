@@ -18,27 +18,41 @@ struct knc_problem {
     unsigned int index_offset;   // knc_set_index_offset: added to every stored neighbour index
     int z_begin, z_end;          // cell planes held (z_end - z_begin == pub.dimz planes LOCALLY)
     int own_z_begin, own_z_end;
-    int dim_global;              // global cubic resolution D (pub.dimx == pub.dimy == D)
-    long long cells;             // D * D * (z_end - z_begin)
+    int dims[3];                 // GLOBAL grid resolution (x, y, z) = pub.dimx / dimy / dimz
+    long long cells;             // dimx * dimy * (z_end - z_begin)
     int query_begin, query_count;
     int solved;
-    float4 *d_points4;           // [n] x, y, z, bits(original index): what the query kernel reads
+    float4 *d_points4;           // [n] x, y, z, bits(own sorted position): what the query kernels read
     unsigned int *d_tags;        // [n] 4th word of every input record in sorted order (point_stride 4 only, else NULL)
-    unsigned int *d_diag;        // [4] restarts, max radius^2 bits, halo misses, spare
+    unsigned int *d_diag;        // [KN_DIAG_WORDS] restarts, max radius^2 bits, halo misses, retry count, block fallbacks
     cudaStream_t stream;
     cudaStream_t copy_stream;    // device->host row copies of knc_solve_to_host (created on first use)
     cudaEvent_t ev[4];
     knc_timings t;
 };
 
-// Grid geometry handed to kernels.
+#define KN_DIAG_WORDS 8
+
+// Grid geometry handed to kernels.  The reference's grid is a cube of D^3 cells (knearests.cu:249); here the three
+// resolutions are independent (kn_problem has dimx / dimy / dimz, knearests.h:5-7): the default grid has cells that
+// are as wide as the first search radius in y and z and narrow in x (knc_fast_dims).
 struct GridGeom {
-    int D;          // global resolution in x and y (and z, globally)
-    int zb, ze;     // cell planes held locally: [zb, ze)
-    float Df;       // (float)D
-    float w;        // cell width 1000 / D
-    float invw;     // D / 1000
+    int Dx, Dy, Dz;       // GLOBAL resolution per axis
+    int zb, ze;           // cell planes held locally: [zb, ze)
+    float Dfx, Dfy, Dfz;  // (float)D per axis -- cellFromPoint multiplies by it (knearests.cu:23-25)
+    float wx, wy, wz;     // cell widths 1000 / D
+    float invwx;          // Dx / 1000
 };
+
+inline GridGeom kn_make_geom(const int dims[3], int zb, int ze) {
+    GridGeom g;
+    g.Dx = dims[0]; g.Dy = dims[1]; g.Dz = dims[2];
+    g.zb = zb; g.ze = ze;
+    g.Dfx = (float)g.Dx; g.Dfy = (float)g.Dy; g.Dfz = (float)g.Dz;
+    g.wx = 1000.f / g.Dfx; g.wy = 1000.f / g.Dfy; g.wz = 1000.f / g.Dfz;
+    g.invwx = g.Dfx / 1000.f;
+    return g;
+}
 
 // ---- grid_build.cu -----------------------------------------------------------------------------
 struct BuildScratch {
@@ -63,6 +77,9 @@ cudaError_t kn_launch_remap_original(const unsigned int *d_knn, const unsigned i
                                      unsigned int *d_out, cudaStream_t st);
 
 // ---- knn_query.cu ------------------------------------------------------------------------------
+// d_retry_list: scratch of kn_retry_ints(query_count) ints (queries handed on to the retry kernel + blocks handed
+// on to the previous-generation select kernel), or NULL for the general kernel alone
+size_t kn_retry_ints(int query_count);
 cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const GridGeom &g, int n, int k,
                             int query_begin, int query_count, float radius0_sq, unsigned int *d_knn,
                             unsigned int *d_diag, int *d_retry_list, int force_general, unsigned int index_offset,

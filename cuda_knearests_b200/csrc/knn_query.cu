@@ -25,8 +25,16 @@
 //  * Candidates are ordered by the 64-bit key bits(d2) << 32 | sorted position: one unsigned compare gives the
 //    total order (d2, position), so the result does not depend on visiting order -- deterministic, and
 //    identical across the three kernels below, across grid densities and across GPUs.
-//  * Three kernels (details at each):
-//      kn_query_select_kernel   k = 8 / 20 / 32 / 50.  Warp-uniform control flow: span lists, lock-step
+//  * Four kernels (details at each):
+//      kn_query_tile_kernel     k = 8 / 20 / 32 / 50 on grids whose y/z cells are at least as wide as the first radius
+//                               (the default grid, knc_fast_dims).  A block of 128 consecutive queries stages the
+//                               3 x 3 x-rows of cells around them ONCE in shared memory with bulk asynchronous copies
+//                               (cp.async.bulk + mbarrier, one copy per row segment), every lane then streams its own
+//                               windows of that tile with 128-bit shared-memory loads, remembers the candidates inside
+//                               its sphere as 16-bit tile slots, selects like the select kernel below and the block's
+//                               rows leave as one bulk copy shared -> global.
+//      kn_query_select_kernel   k = 8 / 20 / 32 / 50, any grid: the previous generation, still the path for blocks
+//                               whose tile does not fit (clustered clouds) and for cubic grids.  Warp-uniform control flow: span lists, lock-step
 //                               streaming of the records through two register buffers, candidates inside the
 //                               sphere are only remembered; one sort-select at the end on 32-bit truncated keys
 //                               (Batcher network in registers) with an exactness guard.
@@ -84,6 +92,10 @@ struct QueryParams {
     const float *ext_queries;  // EXTERNAL mode of the general kernel: query points that are not in the cloud (xyz)
     int *retry_list;       // sorted positions of the queries the fast kernel could not finish
     unsigned int *retry_count;
+    int *block_list;       // blocks (of QB queries) the tile kernel hands to the select kernel; NULL: every block
+    unsigned int *block_count;
+    int halo_cells;        // tile kernel: cells staged beyond the block's own x-range on either side
+    int bulk_rows_ok;      // tile kernel: the row array is 16-byte aligned, rows may leave as one bulk copy
     RowTable tab;
 };
 
@@ -105,10 +117,10 @@ __device__ __forceinline__ QueryGeom query_geom(const float4 me, const GridGeom 
     QueryGeom s;
     s.px = me.x; s.py = me.y; s.pz = me.z;
     // same rounding as the build (knearests.cu:23-28): mul.f32, div.rn.f32, floor
-    s.tx = __fdiv_rn(__fmul_rn(me.x, g.Df), 1000.f);
-    const float ty = __fdiv_rn(__fmul_rn(me.y, g.Df), 1000.f);
-    s.tz = __fdiv_rn(__fmul_rn(me.z, g.Df), 1000.f);
-    s.cj = max(0, min((int)floorf(ty), g.D - 1));
+    s.tx = __fdiv_rn(__fmul_rn(me.x, g.Dfx), 1000.f);
+    const float ty = __fdiv_rn(__fmul_rn(me.y, g.Dfy), 1000.f);
+    s.tz = __fdiv_rn(__fmul_rn(me.z, g.Dfz), 1000.f);
+    s.cj = max(0, min((int)floorf(ty), g.Dy - 1));
     s.ck = max(g.zb, min((int)floorf(s.tz), g.ze - 1));
     s.fy = ty - (float)s.cj;
     s.fz = s.tz - (float)s.ck;
@@ -120,15 +132,15 @@ __device__ __forceinline__ QueryGeom query_geom(const float4 me, const GridGeom 
 // knearests.cu:26-28), so towards that side the cell is unbounded: no gap may be claimed there.  (It
 // matters when the query itself is outside the domain: its own border row then holds points that are
 // closer to it than the nominal cell box is.)
-__device__ __forceinline__ float row_lower_bound2(const QueryGeom &s, int dj, int dk, float w, const GridGeom &g) {
+__device__ __forceinline__ float row_lower_bound2(const QueryGeom &s, int dj, int dk, const GridGeom &g) {
     const int j = s.cj + dj, k = s.ck + dk;
     const float below_y = j > 0 ? (float)dj - s.fy : 0.f;            // query below the row (row's low side bounded)
-    const float above_y = j < g.D - 1 ? s.fy - (float)dj - 1.f : 0.f;  // query above the row
+    const float above_y = j < g.Dy - 1 ? s.fy - (float)dj - 1.f : 0.f;  // query above the row
     const float below_z = k > g.zb ? (float)dk - s.fz : 0.f;
     const float above_z = k < g.ze - 1 ? s.fz - (float)dk - 1.f : 0.f;
     const float gy = fmaxf(0.f, fmaxf(below_y, above_y));
     const float gz = fmaxf(0.f, fmaxf(below_z, above_z));
-    const float ly = fmaxf(0.f, fmaf(gy, w, -kMargin)), lz = fmaxf(0.f, fmaf(gz, w, -kMargin));
+    const float ly = fmaxf(0.f, fmaf(gy, g.wy, -kMargin)), lz = fmaxf(0.f, fmaf(gz, g.wz, -kMargin));
     return (ly * ly + lz * lz) * kShrink;
 }
 
@@ -168,11 +180,11 @@ __device__ __forceinline__ void report_diag(const QueryParams &P, const QueryGeo
     if (finished) {
         rad_bits = __float_as_uint(kd2);
         if (P.g.zb > 0) {
-            const float gap = fmaxf(0.f, (s.tz - (float)P.g.zb) * P.g.w - kMargin);
+            const float gap = fmaxf(0.f, (s.tz - (float)P.g.zb) * P.g.wz - kMargin);
             if (gap * gap * kShrink <= kd2) halo_miss = 1;
         }
-        if (P.g.ze < P.g.D) {
-            const float gap = fmaxf(0.f, ((float)P.g.ze - s.tz) * P.g.w - kMargin);
+        if (P.g.ze < P.g.Dz) {
+            const float gap = fmaxf(0.f, ((float)P.g.ze - s.tz) * P.g.wz - kMargin);
             if (gap * gap * kShrink <= kd2) halo_miss = 1;
         }
     }
@@ -210,8 +222,8 @@ __global__ void __launch_bounds__(QB) kn_query_fast_kernel(const __grid_constant
     unsigned long long *L = smem + tid;                                        // [K][QB] sorted k best
     int2 *SP = reinterpret_cast<int2 *>(smem + (size_t)K * QB) + tid;          // [kSpanSlots][QB] spans
     unsigned long long *QU = smem + (size_t)(K + kSpanSlots) * QB + tid;       // [kQueueSlots][QB] pending
-    const int D = P.g.D, zb = P.g.zb, ze = P.g.ze;
-    const float w = P.g.w, invw = P.g.invw;
+    const int Dx = P.g.Dx, Dy = P.g.Dy, zb = P.g.zb, ze = P.g.ze;
+    const float invw = P.g.invwx;
     const long long row0 = (long long)blockIdx.x * QB;
     const bool valid = row0 + tid < P.query_count;
     const int q = P.query_begin + (int)min(row0 + tid, (long long)P.query_count - 1);
@@ -303,12 +315,12 @@ __global__ void __launch_bounds__(QB) kn_query_fast_kernel(const __grid_constant
                 if (ee < e1 && want && P.tab.lb2[ee] <= bound2) {
                     const int dj = P.tab.dj[ee], dk = P.tab.dk[ee];
                     const int j = s.cj + dj, k = s.ck + dk;
-                    if (j >= 0 && j < D && k >= zb && k < ze) {
-                        const float lbyz2 = row_lower_bound2(s, dj, dk, w, P.g);
+                    if (j >= 0 && j < Dy && k >= zb && k < ze) {
+                        const float lbyz2 = row_lower_bound2(s, dj, dk, P.g);
                         if (lbyz2 <= bound2) {
                             int ilo, ihi;
-                            row_x_range(s, bound2, lbyz2, invw, D, ilo, ihi);
-                            const int row = ((k - zb) * D + j) * D;
+                            row_x_range(s, bound2, lbyz2, invw, Dx, ilo, ihi);
+                            const int row = ((k - zb) * Dy + j) * Dx;
                             alo[u] = row + ilo;
                             ahi[u] = row + ihi + 1;
                             ok[u] = ilo <= ihi;
@@ -405,7 +417,9 @@ __device__ __forceinline__ void load_records_if(float4 (&c)[kSelChunk], int at, 
     }
 }
 
-template <int K_T, int QB, int NET, int CAP>
+// LIST: the blocks to work on are named by P.block_list (what the tile kernel handed over), each resident block takes
+// several in turn; otherwise block b works on queries [b * QB, (b + 1) * QB).
+template <int K_T, int QB, int NET, int CAP, bool LIST>
 __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_constant__ QueryParams P) {
     static_assert(K_T > 0 && K_T + 1 <= NET - 8, "select path: k must leave room for new keys in a round");
     static_assert(NET == 32 || NET == 64, "select path: networks exist for 32 and 64 keys");
@@ -416,9 +430,11 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
     const int tid = threadIdx.x;
     unsigned int *BUF = reinterpret_cast<unsigned int *>(smem) + tid;                                   // [kSelectCap][QB]
     int2 *SP = reinterpret_cast<int2 *>(reinterpret_cast<unsigned int *>(smem) + kSelectCap * QB) + tid;  // [kSpanSlots][QB]
-    const int D = P.g.D, zb = P.g.zb, ze = P.g.ze;
-    const float w = P.g.w, invw = P.g.invw;
-    const long long row0 = (long long)blockIdx.x * QB;
+    const int Dx = P.g.Dx, Dy = P.g.Dy, zb = P.g.zb, ze = P.g.ze;
+    const float invw = P.g.invwx;
+    const unsigned nlist = LIST ? *P.block_count : gridDim.x;
+  for (unsigned bi = blockIdx.x; bi < nlist; bi += gridDim.x) {
+    const long long row0 = (long long)(LIST ? (unsigned)P.block_list[bi] : bi) * QB;
     const bool valid = row0 + tid < P.query_count;
     const int q = P.query_begin + (int)min(row0 + tid, (long long)P.query_count - 1);
     const QueryGeom s = query_geom(__ldg(P.pts + q), P.g);
@@ -443,12 +459,12 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
                 if (ee < e1 && valid && P.tab.lb2[ee] <= r2) {
                     const int dj = P.tab.dj[ee], dk = P.tab.dk[ee];
                     const int j = s.cj + dj, k = s.ck + dk;
-                    if (j >= 0 && j < D && k >= zb && k < ze) {
-                        const float lbyz2 = row_lower_bound2(s, dj, dk, w, P.g);
+                    if (j >= 0 && j < Dy && k >= zb && k < ze) {
+                        const float lbyz2 = row_lower_bound2(s, dj, dk, P.g);
                         if (lbyz2 <= r2) {
                             int ilo, ihi;
-                            row_x_range(s, r2, lbyz2, invw, D, ilo, ihi);
-                            const int row = ((k - zb) * D + j) * D;
+                            row_x_range(s, r2, lbyz2, invw, Dx, ilo, ihi);
+                            const int row = ((k - zb) * Dy + j) * Dx;
                             alo[u] = row + ilo;
                             ahi[u] = row + ihi + 1;
                             ok[u] = ilo <= ihi;
@@ -580,6 +596,277 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
         const int t = idx / K_T, sl = idx - t * K_T;
         out[idx] = OUT[sl * (QB + 1) + t];
     }
+    if (LIST) __syncthreads();  // the staging area is the next block's candidate buffer
+  }
+}
+
+// ======================================================================================== tile path
+// The candidates of a block of QB consecutive queries staged ONCE in shared memory.
+//
+// Precondition (checked by the launcher): the cells are at least as wide in y and z as the first search radius,
+// so a query's sphere cannot reach past the 3 x 3 x-rows of cells around its own row.  QB consecutive queries lie in
+// 1 (sometimes 2 or 3) x-rows of cells; for each such "query row" the block stages the 9 surrounding rows, each
+// cut to the x-range of its queries plus the reach of the sphere: <= 27 SEGMENTS, every one a contiguous run of
+// 16-byte records in global memory, hence one cp.async.bulk each, all completing on one mbarrier.  Lane L of warp 0
+// sets up segment L (two pointer loads, a warp prefix sum for the place in the tile) and issues its copy.
+//
+// While the copies fly every lane works out its own windows ("spans") of those rows as before, in global
+// positions, then rebases them to tile slots.  The scan needs NO bounds test and no predicated load: a span that
+// ends inside a segment is followed by records of the same row that lie beyond the sphere's reach in x (they fail
+// the distance test like any other), a segment is followed by kTilePad records of +inf, and a lane that has run
+// out of spans parks on four +inf records at slot 0 -- so the body is 4 x LDS.128, the arithmetic, and a predicated
+// 16-bit append of the tile slot.  Selection as in the select kernel, keys rebuilt from the tile; the neighbour's
+// sorted position is the 4th word of its record.  The block's rows are laid out in shared memory exactly as in
+// global memory and leave as ONE bulk copy.
+//
+// A block whose queries span more than kTileQueryRows rows, or whose tile would not fit (clustered clouds), names
+// itself in P.block_list and is served by the select kernel afterwards.
+constexpr int kTileQueryRows = 3;
+constexpr int kTileSegs = 9 * kTileQueryRows;  // <= 32: one lane of warp 0 each
+constexpr int kTilePad = 4;                    // +inf records after every segment and at slots 0..3
+
+__device__ __forceinline__ unsigned smem_addr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned arrivals) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(arrivals) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");  // visible to the async proxy
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(unsigned bar, unsigned parity) {
+    unsigned done;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    return done != 0;
+}
+// global -> shared, `bytes` a multiple of 16, both addresses 16-byte aligned; completion counted on the mbarrier
+__device__ __forceinline__ void bulk_load(unsigned dst, const void *src, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+// shared -> global; the caller waits (bulk_store_wait) before the shared memory may go away
+__device__ __forceinline__ void bulk_store(void *dst, unsigned src, unsigned bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(src), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_store_wait() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+template <int K_T, int QB, int NET, int CAP, int TCAP>
+__global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant__ QueryParams P) {
+    static_assert(K_T > 0 && K_T + 1 <= NET - 8, "tile path: k must leave room for new keys in a round");
+    static_assert(NET == 32 || NET == 64, "tile path: networks exist for 32 and 64 keys");
+    static_assert(TCAP < 65536 && TCAP % 8 == 0, "tile slots are stored in 16 bits");
+    static_assert((size_t)TCAP * 16 + (size_t)CAP * QB * 2 >= (size_t)QB * K_T * 4, "row staging reuses tile + buffer");
+    constexpr unsigned kSlotMask = CAP <= 64 ? 63u : 127u;  // low key bits that hold the buffer slot
+    constexpr int kSlotBits = CAP <= 64 ? 6 : 7;
+    static_assert(CAP <= 128, "slot must fit the low key bits");
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ __align__(8) unsigned long long s_bar;
+    __shared__ int s_adj[32];      // per segment: tile slot = s_adj + global sorted position
+    __shared__ int s_ends[4];      // query row and x cell of the block's first and last query
+    __shared__ int s_fallback;
+    const int tid = threadIdx.x, lane = tid & 31;
+    float4 *tile = reinterpret_cast<float4 *>(smem_raw);                                           // [TCAP] records
+    unsigned short *BUF = reinterpret_cast<unsigned short *>(smem_raw + (size_t)TCAP * 16) + tid;   // [CAP][QB] tile slots
+    unsigned *SP = reinterpret_cast<unsigned *>(smem_raw + (size_t)TCAP * 16 + (size_t)CAP * QB * 2) + tid;  // [10][QB] spans
+    const int Dx = P.g.Dx, Dy = P.g.Dy, zb = P.g.zb, ze = P.g.ze;
+    const long long row0 = (long long)blockIdx.x * QB;
+    const int rows = (int)min((long long)QB, (long long)P.query_count - row0);
+    const bool valid = tid < rows;
+    const int q = P.query_begin + (int)row0 + min(tid, rows - 1);
+    const QueryGeom s = query_geom(__ldg(P.pts + q), P.g);
+    const int ci = max(0, min(Dx - 1, (int)floorf(s.tx)));  // the build's cell (same arithmetic, knearests.cu:23-28)
+    const int qrow = (s.ck - zb) * Dy + s.cj;
+    const unsigned bar = smem_addr(&s_bar);
+    if (tid == 0) { mbar_init(bar, 1); s_ends[0] = qrow; s_ends[1] = ci; }
+    if (tid == rows - 1) { s_ends[2] = qrow; s_ends[3] = ci; }
+    __syncthreads();
+    const int qrow0 = s_ends[0], nqr = s_ends[2] - qrow0 + 1;
+    const float4 inf4 = make_float4(__int_as_float(0x7f800000), __int_as_float(0x7f800000), __int_as_float(0x7f800000), 0.f);
+
+    // ---- warp 0: the segments.  Lane = (query row qi, candidate row dj, dk) ------------------------------------
+    if (tid < 32) {
+        int len = 0, g0 = 0;
+        const bool rows_ok = nqr <= kTileQueryRows;
+        if (rows_ok && lane < nqr * 9) {
+            const int qi = lane / 9, rr = lane - 9 * qi, dj = rr % 3 - 1, dk = rr / 3 - 1;
+            const int R = qrow0 + qi, j = R % Dy + dj, k = R / Dy + zb + dk;
+            if (j >= 0 && j < Dy && k >= zb && k < ze) {
+                const int xlo = qi == 0 ? s_ends[1] : 0, xhi = qi == nqr - 1 ? s_ends[3] : Dx - 1;
+                const int xa = max(0, xlo - P.halo_cells), xb = min(Dx - 1, xhi + P.halo_cells);
+                const int base = ((k - zb) * Dy + j) * Dx;
+                g0 = __ldg(P.ptrs + base + xa);
+                len = __ldg(P.ptrs + base + xb + 1) - g0;
+            }
+        }
+        const int need = len > 0 ? len + kTilePad : 0;
+        int incl = need, bytes = len * 16;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += t;
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) bytes += __shfl_xor_sync(0xffffffffu, bytes, d);
+        const int total = __shfl_sync(0xffffffffu, incl, 31) + kTilePad;
+        const int off = kTilePad + incl - need;  // slots 0..3: the parking records
+        const bool ok = rows_ok && total <= TCAP;
+        if (ok) {
+            s_adj[lane] = off - g0;
+            if (len > 0) {
+                bulk_load(smem_addr(tile + off), P.pts + g0, (unsigned)len * 16u, bar);
+#pragma unroll
+                for (int u = 0; u < kTilePad; ++u) tile[off + len + u] = inf4;
+            }
+            if (lane == 0) {
+#pragma unroll
+                for (int u = 0; u < kTilePad; ++u) tile[u] = inf4;
+                mbar_arrive_expect_tx(bar, (unsigned)bytes);
+            }
+        }
+        if (lane == 0) s_fallback = ok ? 0 : 1;
+    }
+
+    // ---- every lane: its windows of the 3 x 3 rows, in global sorted positions -----------------------------------
+    const float r2 = P.radius0_sq;
+    int gb[9], ge[9];
+#pragma unroll
+    for (int rr = 0; rr < 9; ++rr) {
+        const int dj = rr % 3 - 1, dk = rr / 3 - 1;
+        const int j = s.cj + dj, k = s.ck + dk;
+        gb[rr] = 0; ge[rr] = 0;
+        if (valid && j >= 0 && j < Dy && k >= zb && k < ze) {
+            const float lbyz2 = row_lower_bound2(s, dj, dk, P.g);
+            if (lbyz2 <= r2) {
+                int ilo, ihi;
+                row_x_range(s, r2, lbyz2, P.g.invwx, Dx, ilo, ihi);
+                const int base = ((k - zb) * Dy + j) * Dx;
+                gb[rr] = __ldg(P.ptrs + base + ilo);
+                ge[rr] = __ldg(P.ptrs + base + ihi + 1);
+            }
+        }
+    }
+    __syncthreads();
+    if (s_fallback) {  // block-uniform
+        if (tid == 0) P.block_list[atomicAdd(P.block_count, 1u)] = (int)blockIdx.x;
+        return;
+    }
+    const int qi = qrow - qrow0;
+    int nsp = 0;
+#pragma unroll
+    for (int rr = 0; rr < 9; ++rr)
+        if (ge[rr] > gb[rr]) {
+            const int adj = s_adj[qi * 9 + rr];
+            SP[nsp * QB] = (unsigned)(gb[rr] + adj) | ((unsigned)(ge[rr] + adj) << 16);
+            ++nsp;
+        }
+    SP[nsp * QB] = 0u;  // terminator: the parking records at slot 0, recognised by end == 0
+    const int my_slot = q + s_adj[qi * 9 + 4];
+
+    // Append pointer (shared-memory address of the lane's next free buffer entry), clamped once per chunk: a chunk
+    // may run kSelChunk entries past `wlim`, reaching wlim at all counts as an overflow.
+    const unsigned wp0 = smem_addr(BUF);
+    const unsigned wlim = wp0 + (unsigned)(CAP - kSelChunk) * QB * 2u;
+    unsigned wp = wp0;
+
+    while (!mbar_try_wait(bar, 0)) {}  // the tile has landed
+
+    // ---- scan: lock step over the lanes' own span lists, kSelChunk records per iteration --------------------------
+    {
+        const unsigned t0 = SP[0];
+        int ts = (int)(t0 & 0xffffu), end = (int)(t0 >> 16), sp = min(1, nsp);
+        do {
+            float4 c[kSelChunk];
+#pragma unroll
+            for (int u = 0; u < kSelChunk; ++u) c[u] = tile[ts + u];
+#pragma unroll
+            for (int u = 0; u < kSelChunk; ++u) {
+                const float dx = c[u].x - s.px, dy = c[u].y - s.py, dz = c[u].z - s.pz;
+                const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+                asm volatile("{\n\t.reg .pred p;\n\tsetp.le.f32 p, %1, %2;\n\t"
+                             "@p st.shared.u16 [%0], %3;\n\t@p add.u32 %0, %0, %4;\n\t}"
+                             : "+r"(wp)
+                             : "f"(d2), "f"(r2), "r"(ts + u), "n"(QB * 2));
+            }
+            wp = min(wp, wlim);
+            ts += kSelChunk;
+            if (ts >= end) {
+                const unsigned t = SP[sp * QB];
+                ts = (int)(t & 0xffffu); end = (int)(t >> 16);
+                sp = min(sp + 1, nsp);
+            }
+        } while (__any_sync(0xffffffffu, end != 0));
+    }
+
+    // ---- select (see kn_query_select_kernel): 32-bit keys = bits(d2) with the low bits replaced by the buffer slot ----
+    asm volatile("" ::: "memory");  // the appends above were written behind the compiler's back
+    const int cnt = (int)((wp - wp0) / (QB * 2u)) - 1;  // candidates inside the sphere, the query itself not counted
+    const bool searched = valid && cnt >= K_T && wp < wlim;
+    const int have = searched ? cnt + 1 : 0;
+    unsigned a[NET];
+    for (int base = 0, round = 0; round == 0 || __any_sync(0xffffffffu, have > base); ++round) {
+        const int lo = round == 0 ? 0 : K_T + 1;
+#pragma unroll
+        for (int u = 0; u < NET; ++u) {
+            if (u >= lo) {
+                const int slot = base + (u - lo);
+                a[u] = 0xFFFFFFFFu;
+                if (slot < have) {
+                    const int ti = (int)BUF[slot * QB];
+                    const unsigned key = ((unsigned)(make_key(tile[ti], s, 0) >> 32) & ~kSlotMask) | (unsigned)slot;
+                    a[u] = ti == my_slot ? 0xFFFFFFFFu : key;  // self excluded by position, knearests.cu:123
+                }
+            }
+        }
+        base += NET - lo;
+#define KN_CE(i, j)                                     \
+    {                                                   \
+        const unsigned lo_ = min(a[i], a[j]);           \
+        a[j] = max(a[i], a[j]);                         \
+        a[i] = lo_;                                     \
+    }
+        if constexpr (NET == 32) { KN_SORT_NETWORK_32(KN_CE) } else { KN_SORT_NETWORK_64(KN_CE) }
+#undef KN_CE
+    }
+    bool exact = searched;
+#pragma unroll
+    for (int u = 0; u < K_T; ++u) exact = exact && (a[u] >> kSlotBits) < (a[u + 1] >> kSlotBits);
+    if (valid && !exact) P.retry_list[atomicAdd(P.retry_count, 1u)] = q | (cnt < K_T ? (int)0x80000000 : 0);
+    report_diag(P, s, exact, exact ? __uint_as_float((a[K_T - 1] | kSlotMask)) : 0.f, 0u, tid);
+
+    unsigned res[K_T];
+#pragma unroll
+    for (int u = 0; u < K_T; ++u)
+        res[u] = exact ? __float_as_uint(tile[BUF[(a[u] & kSlotMask) * QB]].w) + P.index_offset : KNC_EMPTY;
+
+    // ---- rows: staged in shared memory exactly as they lie in global memory, then one bulk copy ----------------------
+    __syncthreads();  // every lane is done reading the tile and the buffer
+    unsigned *OUT = reinterpret_cast<unsigned *>(smem_raw);
+    if constexpr (K_T % 4 == 0) {
+        uint4 *dst = reinterpret_cast<uint4 *>(OUT + tid * K_T);
+#pragma unroll
+        for (int v = 0; v < K_T / 4; ++v) dst[v] = make_uint4(res[4 * v], res[4 * v + 1], res[4 * v + 2], res[4 * v + 3]);
+    } else {
+        static_assert(K_T % 2 == 0, "row staging writes pairs");
+        uint2 *dst = reinterpret_cast<uint2 *>(OUT + tid * K_T);
+#pragma unroll
+        for (int v = 0; v < K_T / 2; ++v) dst[v] = make_uint2(res[2 * v], res[2 * v + 1]);
+    }
+    unsigned int *out = P.knn + row0 * K_T;
+    const int words = rows * K_T;
+    if (P.bulk_rows_ok && (words & 3) == 0) {  // block-uniform
+        fence_async_smem();  // the staged rows must be visible to the copy engine
+        __syncthreads();
+        if (tid == 0) {
+            bulk_store(out, smem_addr(OUT), (unsigned)words * 4u);
+            bulk_store_wait();
+        }
+    } else {
+        __syncthreads();
+        for (int idx = tid; idx < words; idx += QB) out[idx] = OUT[idx];
+    }
 }
 
 // ===================================================================================== general path
@@ -593,8 +880,8 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
     extern __shared__ unsigned long long smem[];  // [K][QB]: slot-major, thread-minor
     const int K = K_T ? K_T : P.k;
     const int tid = threadIdx.x;
-    const int D = P.g.D, zb = P.g.zb, ze = P.g.ze;
-    const float w = P.g.w, invw = P.g.invw;
+    const int Dx = P.g.Dx, Dy = P.g.Dy, zb = P.g.zb, ze = P.g.ze;
+    const float invw = P.g.invwx, wmin = fminf(P.g.wy, P.g.wz);
     unsigned long long *L = smem + tid;
     const long long total = RETRY ? (long long)*P.retry_count : (long long)P.query_count;
     const long long stride = (long long)gridDim.x * QB;
@@ -618,14 +905,14 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
 
         auto scan_row = [&](int dj, int dk) {
             const int j = s.cj + dj, k = s.ck + dk;
-            if (j < 0 || j >= D || k < zb || k >= ze) return;
-            const float lbyz2 = row_lower_bound2(s, dj, dk, w, P.g);
+            if (j < 0 || j >= Dy || k < zb || k >= ze) return;
+            const float lbyz2 = row_lower_bound2(s, dj, dk, P.g);
             if (lbyz2 > bound2) { pruned = true; return; }
             int ilo, ihi;
-            row_x_range(s, bound2, lbyz2, invw, D, ilo, ihi);
-            if (ilo > 0 || ihi < D - 1) pruned = true;
+            row_x_range(s, bound2, lbyz2, invw, Dx, ilo, ihi);
+            if (ilo > 0 || ihi < Dx - 1) pruned = true;
             if (ilo > ihi) return;
-            const int row = ((k - zb) * D + j) * D;
+            const int row = ((k - zb) * Dy + j) * Dx;
             int p = __ldg(P.ptrs + row + ilo);
             const int end = __ldg(P.ptrs + row + ihi + 1);
             if (p >= end) return;
@@ -663,9 +950,9 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
             // the table ends with its corner rows (lower bound 4 sqrt(2) cells), which lie farther than the face
             // rows of the next ring (5 cells), so leaving the table early says nothing about ring 6.
             {
-                const int rmax = max(max(s.cj, D - 1 - s.cj), max(s.ck - zb, ze - 1 - s.ck));
+                const int rmax = max(max(s.cj, Dy - 1 - s.cj), max(s.ck - zb, ze - 1 - s.ck));
                 for (int r = kTableRing + 1; r <= rmax; ++r) {
-                    const float lb = fmaxf(0.f, (float)(r - 1) * w - kMargin);
+                    const float lb = fmaxf(0.f, (float)(r - 1) * wmin - kMargin);
                     if (lb * lb * kShrink > bound2) { pruned = true; break; }
                     for (int dk = -r; dk <= r; ++dk)
                         for (int dj = -r; dj <= r; dj += (abs(dk) == r ? 1 : 2 * r)) scan_row(dj, dk);
@@ -705,7 +992,7 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
 }
 
 template <int K_T, int QB>
-cudaError_t launch(const QueryParams &P, bool fast, cudaStream_t st) {
+cudaError_t launch(const QueryParams &P, bool fast, bool tile_ok, cudaStream_t st) {
     const size_t list_bytes = sizeof(unsigned long long) * (size_t)P.k * QB;
     const unsigned blocks = (unsigned)(((long long)P.query_count + QB - 1) / QB);
     cudaError_t e;
@@ -721,10 +1008,25 @@ cudaError_t launch(const QueryParams &P, bool fast, cudaStream_t st) {
         if constexpr (kHasSelect) {
             constexpr int NET = K_T <= 20 ? 32 : 64, CAP = K_T <= 20 ? 56 : K_T <= 32 ? 92 : 100;  // 56 and 92: the most that still lets 6 resp. 4 blocks share an SM (228 KB)
             const size_t smem = (sizeof(unsigned) * CAP + sizeof(int2) * kSpanSlots) * QB;
-            e = cudaFuncSetAttribute(kn_query_select_kernel<K_T, QB, NET, CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     (int)smem);
-            if (e != cudaSuccess) return e;
-            kn_query_select_kernel<K_T, QB, NET, CAP><<<blocks, QB, smem, st>>>(P);
+            if (tile_ok) {
+                // tile capacity in records: 9 rows x (QB own + 2 x reach) at one point per cell, + padding, + 4 sigma
+                constexpr int TCAP = K_T <= 8 ? 1472 : K_T <= 20 ? 1536 : K_T <= 32 ? 1600 : 1728;
+                const size_t tsmem = (size_t)TCAP * 16 + (size_t)CAP * QB * 2 + (size_t)10 * QB * 4;
+                e = cudaFuncSetAttribute(kn_query_tile_kernel<K_T, QB, NET, CAP, TCAP>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem);
+                if (e != cudaSuccess) return e;
+                kn_query_tile_kernel<K_T, QB, NET, CAP, TCAP><<<blocks, QB, tsmem, st>>>(P);
+                e = cudaFuncSetAttribute(kn_query_select_kernel<K_T, QB, NET, CAP, true>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                if (e != cudaSuccess) return e;
+                const unsigned list_blocks = blocks < 148u * 4u ? blocks : 148u * 4u;  // loops over the block list
+                kn_query_select_kernel<K_T, QB, NET, CAP, true><<<list_blocks, QB, smem, st>>>(P);
+            } else {
+                e = cudaFuncSetAttribute(kn_query_select_kernel<K_T, QB, NET, CAP, false>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+                if (e != cudaSuccess) return e;
+                kn_query_select_kernel<K_T, QB, NET, CAP, false><<<blocks, QB, smem, st>>>(P);
+            }
         }
         e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)list_bytes);
@@ -750,14 +1052,15 @@ cudaError_t launch(const QueryParams &P, bool fast, cudaStream_t st) {
     return cudaGetLastError();
 }
 
-void fill_table(RowTable &t, float w) {
-    struct Ent { int dj, dk; float lbc2; };
+void fill_table(RowTable &t, float wy, float wz) {
+    struct Ent { int dj, dk; float lbc2, ly, lz; };
     Ent ent[kTableSize];
     int n = 0;
     for (int dk = -kTableRing; dk <= kTableRing; dk++)
         for (int dj = -kTableRing; dj <= kTableRing; dj++) {
             const int a = abs(dj) > 0 ? abs(dj) - 1 : 0, b = abs(dk) > 0 ? abs(dk) - 1 : 0;
-            ent[n++] = {dj, dk, (float)(a * a + b * b)};
+            const float ly = fmaxf(0.f, (float)a * wy - kMargin), lz = fmaxf(0.f, (float)b * wz - kMargin);
+            ent[n++] = {dj, dk, ly * ly + lz * lz, ly, lz};
         }
     // stable insertion sort by (lower bound, Manhattan distance): nearest rows first
     for (int i = 1; i < n; i++) {
@@ -774,8 +1077,7 @@ void fill_table(RowTable &t, float w) {
     for (int i = 0; i < n; i++) {
         t.dj[i] = (signed char)ent[i].dj;
         t.dk[i] = (signed char)ent[i].dk;
-        const float lb = fmaxf(0.f, sqrtf(ent[i].lbc2) * w - kMargin);
-        t.lb2[i] = lb * lb * kShrink;
+        t.lb2[i] = ent[i].lbc2 * kShrink;  // same form as row_lower_bound2 at the nearest corner of the own cell
     }
 }
 
@@ -795,21 +1097,36 @@ cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const Gr
     P.ext_queries = d_ext_queries;
     P.use_select = force_general != 2;  // algorithm 2 = insertion kernel even for small k (A/B, tests)
     P.retry_count = d_diag + 3;
-    fill_table(P.tab, g.w);
-    // The fast kernel searches table rows only: usable when every row outside the table is provably
+    P.block_list = d_retry_list ? d_retry_list + query_count : nullptr;
+    P.block_count = d_diag + 4;
+    fill_table(P.tab, g.wy, g.wz);
+    const float wmin = fminf(g.wy, g.wz), r0 = sqrtf(radius0_sq);
+    // The fast kernels search table rows only: usable when every row outside the table is provably
     // farther than the first-guess radius.
-    const float beyond = fmaxf(0.f, (float)kTableRing * g.w - kMargin);
+    const float beyond = fmaxf(0.f, (float)kTableRing * wmin - kMargin);
     const bool fast = force_general != 1 && d_retry_list && radius0_sq < beyond * beyond * kShrink;
+    // The tile kernel stages the 3 x 3 rows around a query's own: usable when rows two cells away are provably out
+    // of reach (their lower bound is one cell width less the margin), i.e. on grids like knc_fast_dims'.
+    // algorithm 4 = without it (A/B, tests).
+    const float reach = fmaxf(0.f, wmin - kMargin);
+    const bool tile_ok = force_general != 4 && radius0_sq < reach * reach * kShrink;
+    P.halo_cells = (int)ceilf(r0 * kGrow * g.invwx + kMargin * g.invwx + 1e-3f) + 1;  // >= row_x_range's reach, in cells
+    P.bulk_rows_ok = ((uintptr_t)d_knn & 15u) == 0;
     switch (k) {
-        case 8: return launch<8, 128>(P, fast, st);
-        case 20: return launch<20, 128>(P, fast, st);
-        case 32: return launch<32, 128>(P, fast, st);
-        case 50: return launch<50, 128>(P, fast, st);
+        case 8: return launch<8, 128>(P, fast, tile_ok, st);
+        case 20: return launch<20, 128>(P, fast, tile_ok, st);
+        case 32: return launch<32, 128>(P, fast, tile_ok, st);
+        case 50: return launch<50, 128>(P, fast, tile_ok, st);
         default: break;
     }
-    if (k <= 96) return launch<0, 128>(P, fast, st);
-    if (k <= 192) return launch<0, 64>(P, fast, st);
-    return launch<0, 32>(P, fast, st);
+    if (k <= 96) return launch<0, 128>(P, fast, false, st);
+    if (k <= 192) return launch<0, 64>(P, fast, false, st);
+    return launch<0, 32>(P, fast, false, st);
+}
+
+size_t kn_retry_ints(int query_count) {
+    const size_t q = query_count > 0 ? (size_t)query_count : 1;
+    return q + (q + 31) / 32 + 1;  // retried queries + blocks handed from the tile kernel to the select kernel
 }
 
 // d2 of every stored row entry, with the reference's expression (knearests.cu:125 as compiled) -- the reference

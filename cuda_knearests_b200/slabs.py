@@ -27,17 +27,27 @@ import time
 import numpy as np
 
 
-def grid_and_split(n_total: int, world: int, density: float = 3.1):
-    """Global grid resolution and plane ownership: zsplit[r] = r * D // world."""
+def grid_and_split(n_total: int, world: int, k: int = 0, density: float = 0.0):
+    """Global grid resolution (x, y, z) and plane ownership: zsplit[r] = r * Dz // world.  density > 0: the cube
+    with that many points per cell (3.1: the reference's, knearests.cu:249); else the library's own grid for k."""
     import cuda_knearests_b200 as K
-    D = K.grid_dim(n_total, density)
-    return D, [(r * D) // world for r in range(world + 1)]
+    if density > 0:
+        D = K.grid_dim(n_total, density)
+        dims = (D, D, D)
+    else:
+        dims = K.fast_dims(n_total, k)
+    return dims, [(r * dims[2]) // world for r in range(world + 1)]
 
 
-def halo_planes(k: int, density: float = 3.1) -> int:
-    """Planes of halo on each side: 1.75 x the first-guess search radius, in cells (SURVEY 8e table:
-    k = 8 / 20 / 32 / 50 -> 2 / 3 / 3 / 4).  Verified after the solve, widened if it was not enough."""
+def halo_planes(k: int, n_total: int | None = None, planes: int | None = None, density: float = 3.1) -> int:
+    """Planes of halo on each side: 1.75 x the first-guess search radius, in planes.  With n_total and the number
+    of z planes of the grid: for that grid (2 on the library's own grid, whose planes are as thick as the radius);
+    without: for the cube of `density` points per cell (k = 8 / 20 / 32 / 50 -> 2 / 3 / 3 / 4 at
+    3.1).  Verified after the solve, widened if it was not enough."""
     lam = k + 2.5 * math.sqrt(k) + 2.0
+    if n_total is not None and planes is not None:
+        r0 = (3.0 * lam / (4.0 * math.pi * (n_total / 1e9))) ** (1.0 / 3.0)
+        return max(2, math.ceil(1.75 * r0 / (1000.0 / planes)))
     r0_cells = (3.0 * lam / (4.0 * math.pi * density)) ** (1.0 / 3.0)
     return max(2, math.ceil(1.75 * r0_cells))
 
@@ -202,7 +212,7 @@ class _DevView:
 
 
 def solve_distributed(local_xyz, first_id: int, n_total: int, k: int, group=None, halo: int | None = None,
-                      density: float = 3.1, phases: dict | None = None, host_rows=None,
+                      density: float = 0.0, phases: dict | None = None, host_rows=None,
                       peers: PeerExchange | None = None) -> SlabRows:
     """One pass of the multi-GPU hot path on this rank's chunk (CUDA tensor [n_local, 3]).
     `phases` (optional dict) receives wall-clock milliseconds per phase, with a device sync after each
@@ -214,9 +224,10 @@ def solve_distributed(local_xyz, first_id: int, n_total: int, k: int, group=None
     import torch.distributed as dist
     import cuda_knearests_b200 as K
     world, rank = dist.get_world_size(group), dist.get_rank(group)
-    D, zsplit = grid_and_split(n_total, world, density)
-    halo = halo_planes(k, density) if halo is None else halo
-    info = {"grid_dim": D, "zsplit": zsplit, "attempts": 0}
+    dims, zsplit = grid_and_split(n_total, world, k, density)
+    D = dims[2]  # planes
+    halo = halo_planes(k, n_total, D) if halo is None else halo
+    info = {"grid_dim": list(dims), "zsplit": zsplit, "attempts": 0}
     t_last = [time.perf_counter()]
     dev = local_xyz.device
 
@@ -245,7 +256,7 @@ def solve_distributed(local_xyz, first_id: int, n_total: int, k: int, group=None
         p = None
         mine = [0, 0]
         if oze > ozb and recv_xyz.shape[0] > 0:
-            p = K.KnProblem(recv_xyz, k=k, grid_dim=D, slab=(zb, ze, ozb, oze), density=density)
+            p = K.KnProblem(recv_xyz, k=k, grid_dims=dims, slab=(zb, ze, ozb, oze))
             mine = [p.info.query_count, p.info.query_begin]
         mark("prepare")
         # global sorted position of a local one = local + (queries of all lower ranks - own query_begin)
@@ -308,7 +319,7 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
                 print(f"bench: {e}; using the staged NCCL exchange", file=sys.stderr)
 
     def step():
-        r = solve_distributed(pts, lo, n, k, density=args.density or 3.1, peers=peers)
+        r = solve_distributed(pts, lo, n, k, density=args.density, peers=peers)
         info = r.info
         r.free()
         return info
@@ -335,7 +346,7 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
         del rr  # or its permutation block is still held and the pass below pays a cudaMalloc for another
         torch.cuda.synchronize()
         tt = time.perf_counter()
-        rr = solve_distributed(pts, lo, n, k, density=args.density or 3.1, phases=phase_ms, peers=peers)
+        rr = solve_distributed(pts, lo, n, k, density=args.density, phases=phase_ms, peers=peers)
         torch.cuda.synchronize()
         t1 = time.perf_counter()
         rr.free()
@@ -348,11 +359,11 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
     allstats = [torch.empty_like(stats) for _ in range(world)]
     dist.all_gather(allstats, stats)
 
-    # after the timed region: every rank has the caller's checker (bench.py: the CPU oracle) look at sampled rows of
-    # one more pass -- rows in global sorted positions, the id table (tags) and the cell pointers of its slab
+    # after the timed region: every rank hands sampled rows of one more pass to the checker the caller passed in
+    # (bench.py) -- rows in global sorted positions, the id table (tags) and the cell pointers of its slab
     checks = [None] * world
     if verify is not None:
-        r = solve_distributed(pts, lo, n, k, density=args.density or 3.1, peers=peers)
+        r = solve_distributed(pts, lo, n, k, density=args.density, peers=peers)
         mine = {"queries": 0, "mismatches": 0}
         if r.handle is not None:
             i = r.handle.info
@@ -374,7 +385,7 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
 
         def step_e2e():
             d_in = host_in.to(dev, non_blocking=True)
-            r = solve_distributed(d_in, lo, n, k, density=args.density or 3.1, host_rows=host_rows_np, peers=peers)
+            r = solve_distributed(d_in, lo, n, k, density=args.density, host_rows=host_rows_np, peers=peers)
             nq = r.rows.shape[0]
             host_qid[:nq].copy_(r.permutation, non_blocking=True)
             torch.cuda.synchronize()
@@ -403,15 +414,16 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
         worst = max(range(world), key=lambda r: float(allstats[r][0].item()))
         achieved = (12 + 4 * k) * queries[worst] / (float(allstats[worst][0].item()) * 1e-3) / 1e9
         cfg = workload_config(args)
-        cfg.update(parallelism=f"z-slabs x{world}", halo_planes=infos[-1]["halo"], grid_dim=infos[-1]["grid_dim"],
-                   points_held_per_rank=[int(s[3].item()) for s in allstats],
-                   records_sent_per_rank=[int(s[4].item()) for s in allstats],
-                   exchange=("routing kernel stores every group straight into the destination GPU's receive buffer over "
-                             "NVLink (CUDA IPC peer memory) + all-gather of the group sizes + barrier, inside the timed step"
-                             if peers is not None else "NCCL all_to_all_single of 16-byte records, inside the timed step"))
+        layout = dict(halo_planes=infos[-1]["halo"], grid_dims=infos[-1]["grid_dim"],
+                      points_held_per_rank=[int(s[3].item()) for s in allstats],
+                      records_sent_per_rank=[int(s[4].item()) for s in allstats],
+                      exchange=("routing kernel stores every group straight into the destination GPU's receive buffer over "
+                                "NVLink (CUDA IPC peer memory) + all-gather of the group sizes + barrier, inside the timed step"
+                                if peers is not None else "NCCL all_to_all_single of 16-byte records, inside the timed step"))
         line = {"metric": METRIC, "value": n / (wall / args.steps), "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+                "layout": layout,
                 "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 14 * args.steps * world,  # per rank: route 3, build 6 (+3 z-band split when the slab is large), query 2
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": None, "kernel": "kn_query_select_kernel (slowest rank)",

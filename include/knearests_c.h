@@ -46,11 +46,12 @@ typedef struct knc_problem knc_problem; /* opaque; its first bytes are a kn_prob
 typedef struct {
     size_t struct_size;
     int k;                  /* neighbours per point; default = library's DEFAULT_NB_PLANES (params.h:4) */
-    float density;          /* target points per grid cell; default 3.1f (knearests.cu:249)             */
+    float density;          /* > 0: a CUBIC grid with this many points per cell, D = round(cbrt(n / density))
+                               -- 3.1f gives the reference's grid (knearests.cu:249).  0: see grid_dims     */
     int points_on_device;   /* 1: `xyz` is a DEVICE pointer on the current device (no H2D copy)         */
-    int grid_dim;           /* force the cubic grid resolution D (default: from n and density)          */
+    int grid_dim;           /* force the cubic grid resolution D                                        */
     /* z-slab mode (multi-GPU): the handle holds only cell planes [z_begin, z_end) of a
-     * global D^3 grid (grid_dim must be set) and answers queries only for the points in planes
+     * global grid (grid_dim or grid_dims must be set) and answers queries only for the points in planes
      * [own_z_begin, own_z_end); the other planes are a read-only halo.  All zero = whole grid. */
     int z_begin, z_end;
     int own_z_begin, own_z_end;
@@ -60,6 +61,12 @@ typedef struct {
                                pre-pass (testing, A/B)                                                  */
     int point_stride;       /* floats per input point: 3 (xyz, default) or 4 (xyz + one word that is carried
                                along, see knc_get_tags; e.g. the records knc_slab_route writes)         */
+    int grid_dims[3];       /* force the grid resolution per axis (x, y, z; all three > 0).  The reference's grid
+                               is a cube (knearests.cu:249) but its handle has dimx / dimy / dimz
+                               (knearests.h:5-7) and nothing in its API depends on the cube.  Precedence:
+                               grid_dims, grid_dim, density, environment KN_GRID_DENSITY, else knc_fast_dims(n, k).
+                               The grid decides the cell order (hence the permutation and the row numbering),
+                               never which neighbours a point gets.                                       */
 } knc_options;
 
 /* What the handle holds; device pointers are valid until knc_free. */
@@ -72,7 +79,7 @@ typedef struct {
     int query_count;        /* number of queries = rows of d_knearests                                  */
     int solved;             /* 1 after knc_solve                                                        */
     const float *d_points;          /* [n*3]  sorted points, AoS xyz (kn_problem.d_stored_points)       */
-    const float *d_points4;         /* [n*4]  sorted points as x,y,z,bits(original index)               */
+    const float *d_points4;         /* [n*4]  sorted points as x,y,z,bits(own sorted position)          */
     const unsigned int *d_permutation; /* [n]                                                           */
     const int *d_counters;          /* [cells]                                                          */
     const int *d_ptrs;              /* [cells + 1]                                                      */
@@ -168,8 +175,16 @@ int knc_get_stats(knc_problem *p, knc_stats *out);
 int knc_get_info(knc_problem *p, knc_info *out);
 int knc_get_timings(knc_problem *p, knc_timings *out);
 
-/* Grid resolution the engine would choose: max(1, round(cbrt(n / density))) (knearests.cu:249). */
+/* Resolution of the cubic grid for a number of points per cell: max(1, round(cbrt(n / density)))
+ * (knearests.cu:249; density <= 0 means the reference's 3.1). */
 int knc_grid_dim(int n, float density);
+
+/* The grid the library chooses when the caller names none: dims[0..2] = cells in x, y, z.  Cells are 2 % wider in
+ * y and z than the first search radius (the sphere expected to hold k + 2.5 sqrt(k) + 2 points of a uniform cloud)
+ * and narrow in x, about one point per cell: a query then needs the 3 x 3 x-rows of cells around its own and
+ * nothing else, which is the tile the query kernel stages in shared memory.  k <= 0: the default k.  The reference
+ * sizes a cube for 3.1 points per cell (knearests.cu:249); KN_GRID_DENSITY=3.1 or density = 3.1f restores it. */
+int knc_fast_dims(int n, int k, int *dims);
 
 /* Message of the last failure on the calling thread ("" if none). */
 const char *knc_last_error(void);

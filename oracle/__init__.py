@@ -61,6 +61,8 @@ def lib() -> C.CDLL:
         L.kno_knn_exact.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, _i32p, _f32p, C.c_int, _u32p,
                                     C.c_void_p]
         L.kno_knn_exact.restype = None
+        L.kno_fast_dims.argtypes = [C.c_int, C.c_int, C.POINTER(C.c_int)]
+        L.kno_fast_dims.restype = None
         L.kno_brute.argtypes = [_f32p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _u32p, C.c_void_p]
         L.kno_brute.restype = None
         L.kno_brute_external.argtypes = [_f32p, C.c_int, _f32p, C.c_int, C.c_int, _u32p, C.c_void_p]
@@ -102,30 +104,48 @@ def load_xyz(path: str, normalize: bool = True) -> np.ndarray:
     return xyz[:n].copy()
 
 
-class Grid:
-    """Deterministic grid build (knearests.cu:32-60 made canonical, see knn_oracle.c)."""
+def fast_dims(n: int, k: int) -> tuple:
+    """The engine's default grid resolution per axis, restated (kno_fast_dims)."""
+    d = (C.c_int * 3)()
+    lib().kno_fast_dims(int(n), int(k), d)
+    return int(d[0]), int(d[1]), int(d[2])
 
-    def __init__(self, xyz: np.ndarray, density: float = 3.1, dim: int | None = None):
+
+class Grid:
+    """Deterministic grid build (knearests.cu:32-60 made canonical, see knn_oracle.c).  The grid is the reference's
+    cube for `density` points per cell (knearests.cu:249) unless `dim` (cube) or `dims` (x, y, z) name it."""
+
+    def __init__(self, xyz: np.ndarray, density: float = 3.1, dim: int | None = None, dims=None):
         xyz = np.ascontiguousarray(xyz, np.float32).reshape(-1, 3)
         self.n = n = xyz.shape[0]
-        self.dim = D = int(dim) if dim else grid_dim(n, density)
-        self.counters = np.zeros(D ** 3, np.int32)
-        self.ptrs = np.zeros(D ** 3 + 1, np.int32)
+        if dims is not None:
+            self.dims = tuple(int(v) for v in dims)
+        else:
+            D = int(dim) if dim else grid_dim(n, density)
+            self.dims = (D, D, D)
+        self.dim = self.dims[0] if self.dims[0] == self.dims[1] == self.dims[2] else None
+        dx, dy, dz = self.dims
+        cells = dx * dy * dz
+        self.counters = np.zeros(cells, np.int32)
+        self.ptrs = np.zeros(cells + 1, np.int32)
         self.sorted_xyz = np.empty((n, 3), np.float32)
         self.permutation = np.empty(n, np.uint32)
-        lib().kno_build(xyz, n, D, D, D, self.counters, self.ptrs, self.sorted_xyz, self.permutation)
+        lib().kno_build(xyz, n, dx, dy, dz, self.counters, self.ptrs, self.sorted_xyz, self.permutation)
 
     def knn_exact(self, K: int, with_d2: bool = False):
         """Engine contract: rows by sorted position, ascending (d2_gpu, sorted position)."""
         out = np.empty((self.n, K), np.uint32)
         d2 = np.empty((self.n, K), np.float32) if with_d2 else None
-        lib().kno_knn_exact(self.dim, self.dim, self.dim, self.n, self.ptrs, self.sorted_xyz, K, out,
+        dx, dy, dz = self.dims
+        lib().kno_knn_exact(dx, dy, dz, self.n, self.ptrs, self.sorted_xyz, K, out,
                             d2.ctypes.data if with_d2 else None)
         return (out, d2) if with_d2 else out
 
     def knn_refwalk(self, K: int):
         """Faithful restatement of the reference's knearest kernel (knearests.cu:93-148)."""
         D = self.dim
+        if D is None:
+            raise ValueError("the reference's walk is defined on its cubic grid only")
         if D < 16:  # knearests.cu:255-258
             raise ValueError("reference does not support low number of input points")
         offs = np.empty(16 ** 4, np.int32)

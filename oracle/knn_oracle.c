@@ -230,6 +230,16 @@ static inline int kno_ent_less(float d, unsigned p, const kno_ent *e) {
 
 void kno_knn_exact(int xdim, int ydim, int zdim, int n, const int *ptrs,
                    const float *sorted_xyz, int K, unsigned *knn, float *knn_d2 /* may be NULL */) {
+    /* The reference's grid is a cube and its rings are Chebyshev shells of whole cells (:262-277).  For a grid with
+     * different resolutions per axis the shells are kept equally thick in SPACE: shell t is the box of cells within
+     * ext_a(t) = ceil(t * wmax / w_a) cells of the query's cell along axis a, minus the box of shell t-1 (for a
+     * cube ext = t: the reference's rings).  A cell outside box t is more than ext_a(t) cells away along some axis
+     * a, so every point in it is at least ext_a(t) * w_a >= t * wmax away. */
+    const float wx = 1000.f / (float)xdim, wy = 1000.f / (float)ydim, wz = 1000.f / (float)zdim;
+    float wmax = wx > wy ? wx : wy;
+    if (wz > wmax) wmax = wz;
+    int dmin = xdim < ydim ? xdim : ydim;
+    if (zdim < dmin) dmin = zdim;
     int dmax = xdim > ydim ? xdim : ydim;
     if (zdim > dmax) dmax = zdim;
 #pragma omp parallel for schedule(dynamic, 1024)
@@ -238,20 +248,25 @@ void kno_knn_exact(int xdim, int ydim, int zdim, int n, const int *ptrs,
         int cnt = 0;
         float px = sorted_xyz[3 * q], py = sorted_xyz[3 * q + 1], pz = sorted_xyz[3 * q + 2];
         int ci = kno_axis_cell(px, xdim), cj = kno_axis_cell(py, ydim), ck = kno_axis_cell(pz, zdim);
+        int pex = -1, pey = -1, pez = -1; /* extents of the previous shell's box */
         for (int ring = 0; ring <= dmax; ring++) {
             if (cnt == K && ring >= 1) {
-                /* :278-279 bound, shrunk by 0.1% of a cell so that f32 rounding at cell borders can
-                 * never end the walk early; visiting extra rings cannot change a total-order result */
-                float w = 1000.f / (float)dmax;
-                float b = (float)(1000. * (double)(float)(ring - 1) / (double)(float)dmax) - 1e-3f * w;
+                /* :278-279 bound (distance to the shell = (ring-1) shell widths), shrunk by 0.1% of a cell so that
+                 * f32 rounding at cell borders can never end the walk early; visiting extra shells cannot change
+                 * a total-order result */
+                float b = (float)((double)(float)(ring - 1) * (double)wmax) - 1e-3f * wmax;
                 if (b > 0.f && best[K - 1].d < b * b) break;
             }
-            for (int k = ck - ring; k <= ck + ring; k++) {
+            int ex = (int)ceil((double)ring * wmax / wx - 1e-9), ey = (int)ceil((double)ring * wmax / wy - 1e-9),
+                ez = (int)ceil((double)ring * wmax / wz - 1e-9);
+            if (pex >= xdim && pey >= ydim && pez >= zdim) break; /* the whole grid has been visited */
+            for (int k = ck - ez; k <= ck + ez; k++) {
                 if (k < 0 || k >= zdim) continue;
-                for (int j = cj - ring; j <= cj + ring; j++) {
+                for (int j = cj - ey; j <= cj + ey; j++) {
                     if (j < 0 || j >= ydim) continue;
-                    int face = (abs(k - ck) == ring) || (abs(j - cj) == ring);
-                    for (int i = ci - ring; i <= ci + ring; i += (face ? 1 : (ring ? 2 * ring : 1))) {
+                    int inner_yz = abs(k - ck) <= pez && abs(j - cj) <= pey; /* inside the previous box in y and z */
+                    for (int i = ci - ex; i <= ci + ex; i++) {
+                        if (inner_yz && abs(i - ci) <= pex) { i = ci + pex; continue; } /* skip the previous box */
                         if (i < 0 || i >= xdim) continue;
                         long cell = i + (long)j * xdim + (long)k * xdim * ydim;
                         for (int p = ptrs[cell]; p < ptrs[cell + 1]; p++) {
@@ -270,12 +285,30 @@ void kno_knn_exact(int xdim, int ydim, int zdim, int n, const int *ptrs,
                     }
                 }
             }
+            pex = ex; pey = ey; pez = ez;
         }
         for (int i = 0; i < K; i++) {
             knn[(size_t)q * K + i] = i < cnt ? best[i].p : KNO_EMPTY;
             if (knn_d2) knn_d2[(size_t)q * K + i] = i < cnt ? best[i].d : FLT_MAX;
         }
     }
+    (void)dmin;
+}
+
+/* The engine's default grid (no reference counterpart: the reference sizes a cube for 3.1 points per cell,
+ * knearests.cu:249).  Restated from the rule in include/knearests_c.h (knc_fast_dims): y and z cells 2 % wider
+ * than the radius r0 of the sphere expected to hold k + 2.5 sqrt(k) + 2 points of a uniform cloud of n points in
+ * [0,1000]^3, and one cell per point overall. */
+void kno_fast_dims(int n, int k, int *dims) {
+    double lambda = k + 2.5 * sqrt((double)k) + 2.0;
+    double r0 = cbrt(3.0 * lambda / (4.0 * 3.14159265358979323846 * ((double)n / 1e9)));
+    int dyz = (int)floor(1000.0 / (1.02 * r0));
+    if (dyz < 1) dyz = 1;
+    if (dyz > 1024) dyz = 1024;
+    long long dx = llround((double)n / ((double)dyz * dyz));
+    if (dx < 1) dx = 1;
+    if (dx > 1048576) dx = 1048576;
+    dims[0] = (int)dx; dims[1] = dyz; dims[2] = dyz;
 }
 
 /* Brute force O(n*m) in an arbitrary index space (no grid at all): for queries q in [q0,q1) the K

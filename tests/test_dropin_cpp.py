@@ -34,17 +34,24 @@ def test_dropin_binary_links_against_the_reference_symbols():
 def test_dropin_caller_gets_the_oracle_rows(oracle, pts20k, tmp_path):
     if not BIN.exists():
         build_dropin()
+    import os
     pts20k.tofile(tmp_path / "points.f32")
-    r = subprocess.run([str(BIN), str(tmp_path / "points.f32"), str(tmp_path / "neighbors.u32")],
-                       capture_output=True, text=True)
-    assert r.returncode == 0, r.stderr
-    assert "Grid:  points per cell: 0 (min), 8 (max)" in r.stderr  # kn_print_stats, as the reference prints it
-    assert "[3] => 2091" in r.stderr
-    got = np.fromfile(tmp_path / "neighbors.u32", np.uint32).reshape(-1, 50)
-    g = oracle.Grid(pts20k)
-    want = np.empty_like(got)
-    want[g.permutation] = g.permutation[g.knn_exact(50)]
-    assert np.array_equal(got, want)
+    # (1) on the reference's grid (KN_GRID_DENSITY=3.1: 19^3 cells for this fixture): kn_print_stats
+    #     prints the reference's numbers; (2) on the library's own grid: other cell statistics, the same neighbours
+    for env, g in (({"KN_GRID_DENSITY": "3.1"}, oracle.Grid(pts20k)),
+                   ({}, oracle.Grid(pts20k, dims=oracle.fast_dims(len(pts20k), 50)))):
+        r = subprocess.run([str(BIN), str(tmp_path / "points.f32"), str(tmp_path / "neighbors.u32")],
+                           capture_output=True, text=True, env={**os.environ, **env})
+        assert r.returncode == 0, r.stderr
+        if env:
+            assert "Grid:  points per cell: 0 (min), 8 (max)" in r.stderr  # kn_print_stats, as the reference prints it
+            assert "[3] => 2091" in r.stderr
+        else:
+            assert "Grid:  points per cell: " in r.stderr
+        got = np.fromfile(tmp_path / "neighbors.u32", np.uint32).reshape(-1, 50)
+        want = np.empty_like(got)
+        want[g.permutation] = g.permutation[g.knn_exact(50)]
+        assert np.array_equal(got, want)
 
 
 @pytest.mark.gpu
@@ -69,7 +76,7 @@ def test_cli_driver_loads_xyz_like_the_reference_and_prints_its_lines(oracle, tm
     pts = np.fromfile(tmp_path / "pts.f32", np.float32).reshape(-1, 3)
     assert np.array_equal(pts, oracle.load_xyz(str(xyz)))  # loader == restated reference loader, bit for bit
     got = np.fromfile(tmp_path / "nb.u32", np.uint32).reshape(-1, 50)
-    g = oracle.Grid(pts)
+    g = oracle.Grid(pts, dims=oracle.fast_dims(len(pts), 50))
     want = np.empty_like(got)
     want[g.permutation] = g.permutation[g.knn_exact(50)]
     assert np.array_equal(got, want)

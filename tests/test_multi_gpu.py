@@ -18,7 +18,8 @@ def test_route_kernel_is_the_stable_multisplit(kn, oracle):
     from cuda_knearests_b200 import slabs
     n, world = 300_000, 4
     pts = oracle.generate_uniform(n, seed=31)
-    D, zsplit = slabs.grid_and_split(1_200_000, world)
+    dims, zsplit = slabs.grid_and_split(1_200_000, world, density=3.1)
+    D = dims[2]
     dev = torch.from_numpy(pts).cuda()
     for halo in (0, 3, 40):
         rec, counts = slabs.route_device(dev, 5_000_000, D, zsplit, halo)
@@ -40,8 +41,9 @@ def test_emulated_ranks_reproduce_single_gpu_rows(kn, oracle, world, k, n):
     with kn.KnProblem(pts, k=k, algorithm=3 if n > 20_000_000 else 0) as p:  # big case: reference rows without the pre-pass
         p.solve()
         want_rows, want_perm, want_orig = p.get_knearests(), p.get_permutation(), p.get_knearests_original()
-    D, zsplit = slabs.grid_and_split(n, world)
-    halo = slabs.halo_planes(k)
+    dims, zsplit = slabs.grid_and_split(n, world, k)  # the library's own grid, as the multi-GPU driver uses it
+    D = dims[2]
+    halo = slabs.halo_planes(k, n, D)
     dev = torch.from_numpy(pts).cuda()
     routed = []
     for r in range(world):
@@ -55,7 +57,7 @@ def test_emulated_ranks_reproduce_single_gpu_rows(kn, oracle, world, k, n):
         rx = torch.cat([rec[off[d]:off[d + 1]] for rec, off in routed]).contiguous()  # [m,4] records
         ids_ptr = C.c_void_p(rx.data_ptr() + 12)                                       # id words, stride 4
         zb, ze, ozb, oze = slabs.held_planes(zsplit, d, halo, D)
-        with kn.KnProblem(rx, k=k, grid_dim=D, slab=(zb, ze, ozb, oze)) as p:
+        with kn.KnProblem(rx, k=k, grid_dims=dims, slab=(zb, ze, ozb, oze)) as p:
             nq = p.info.query_count
             # original ids first (no offset), then the global-position form
             p.solve()

@@ -39,8 +39,9 @@ def _worker(rank, world, port, n, k, out_dir):
     from cuda_knearests_b200 import slabs
     dist.init_process_group("gloo", rank=rank, world_size=world)
     pts = O.generate_uniform(n, seed=77)
-    D, zsplit = slabs.grid_and_split(n, world)
-    halo = slabs.halo_planes(k)
+    dims, zsplit = slabs.grid_and_split(n, world, k)
+    D = dims[2]
+    halo = slabs.halo_planes(k, n, D)
     lo, hi = rank * n // world, (rank + 1) * n // world
     rec, counts = numpy_route(pts[lo:hi], lo, D, zsplit, halo)
     rrec, rc = slabs.exchange(torch.from_numpy(rec), counts)
@@ -81,9 +82,14 @@ def test_plan_matches_survey():
     from cuda_knearests_b200 import slabs
     # halo 2 / 3 / 3 / 4 planes for k = 8 / 20 / 32 / 50
     assert [slabs.halo_planes(k) for k in (8, 20, 32, 50)] == [2, 3, 3, 4]
-    D, zs = slabs.grid_and_split(100_000_000, 8)
-    assert D == 318 and zs[0] == 0 and zs[-1] == 318
+    dims, zs = slabs.grid_and_split(100_000_000, 8, density=3.1)
+    D = dims[2]
+    assert dims == (318, 318, 318) and zs[0] == 0 and zs[-1] == 318
     sizes = np.diff(zs)
     assert sizes.min() >= 39 and sizes.max() <= 40          # 318 planes over 8 ranks
     assert slabs.held_planes(zs, 0, 3, D) == (0, zs[1] + 3, 0, zs[1])
     assert slabs.held_planes(zs, 7, 3, D) == (zs[7] - 3, 318, zs[7], 318)
+    # the library's own grid: planes as thick as the first search radius, so 2 planes of halo for every k
+    for k in (8, 20, 32, 50):
+        dims, zs = slabs.grid_and_split(100_000_000, 8, k)
+        assert dims[1] == dims[2] and zs[-1] == dims[2] and slabs.halo_planes(k, 100_000_000, dims[2]) == 2

@@ -138,3 +138,28 @@ def test_exact_equals_brute_force_on_random_shapes(oracle):
         pts = np.ascontiguousarray(make_cloud(rng, kind, n), np.float32)
         g = oracle.Grid(pts, density=density)
         assert np.array_equal(g.knn_exact(k), oracle.brute(g.sorted_xyz, k)), (case, kind, n, k, density)
+
+
+def test_exact_walk_on_non_cubic_grids_equals_brute_force(oracle):
+    """The engine's default grid is not a cube (narrow x cells, y/z cells as wide as the search radius): the oracle's
+    exact walk generalises the reference's Chebyshev rings to box shells of equal thickness in space, and must give
+    the brute-force rows on any resolution triple -- including degenerate ones."""
+    pts = oracle.generate_uniform(40_000, seed=3)
+    want_idx, _ = oracle.canonical_rows(oracle.brute(pts, 20), None, pts)
+    for dims in [oracle.fast_dims(len(pts), 20), oracle.fast_dims(len(pts), 50), (103, 12, 12), (7, 40, 19), (1, 1, 1),
+                 (300, 5, 5), (2, 3, 500)]:
+        g = oracle.Grid(pts, dims=dims)
+        assert g.dims == tuple(dims) and int(g.ptrs[-1]) == len(pts)
+        idx, _ = oracle.canonical_rows(g.knn_exact(20), g.permutation, pts)
+        assert np.array_equal(idx, want_idx), dims
+
+
+def test_default_grid_rule_is_the_same_in_library_and_oracle(kn, oracle):
+    """knc_fast_dims (host code of the library, no GPU needed) against the oracle's restatement of the rule."""
+    for n in (1, 2, 100, 11_545, 20_626, 300_000, 10_000_000, 100_000_000, 125_000_000, 1_000_000_000, 2_000_000_000):
+        for k in (1, 8, 20, 32, 50, 100, 256):
+            assert kn.fast_dims(n, k) == oracle.fast_dims(n, k), (n, k)
+    dx, dy, dz = kn.fast_dims(100_000_000, 20)
+    assert dy == dz and 0.9 < dx * dy * dz / 1e8 < 1.1               # about one cell per point
+    r0 = (3 * (20 + 2.5 * 20 ** 0.5 + 2) / (4 * np.pi * 0.1)) ** (1 / 3)
+    assert 1.0 < (1000 / dy) / r0 < 1.05                              # y/z cells just wider than the first radius

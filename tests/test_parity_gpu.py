@@ -17,12 +17,22 @@ def run_engine(kn, pts, K, **kw):
     with kn.KnProblem(pts, k=K, **kw) as p:
         p.solve()
         return {"knn": p.get_knearests(), "perm": p.get_permutation(), "points": p.get_points(),
-                "stats": p.stats(), "dim": p.info.dimx, "timings": p.timings(), "info": p.info}
+                "stats": p.stats(), "dims": (p.info.dimx, p.info.dimy, p.info.dimz), "timings": p.timings(),
+                "info": p.info, "k": K}
+
+
+def default_grid(oracle, pts, K):
+    """The oracle's build on the grid the library chooses when the caller names none (knc_fast_dims, restated in
+    oracle/knn_oracle.c:kno_fast_dims)."""
+    return oracle.Grid(pts, dims=oracle.fast_dims(len(pts), K))
+
+
+REFERENCE_GRID = {"density": 3.1}  # the reference's cube, knearests.cu:249 (engine and oracle take the same keyword)
 
 
 def assert_layout_equals_oracle(oracle, pts, res, **gridkw):
-    g = oracle.Grid(pts, **gridkw)
-    assert res["dim"] == g.dim
+    g = oracle.Grid(pts, **gridkw) if gridkw else default_grid(oracle, pts, res["k"])
+    assert res["dims"] == g.dims
     assert np.array_equal(res["perm"], g.permutation)          # stable counting sort, knearests.cu:51-60
     assert np.array_equal(res["points"], g.sorted_xyz)
     hist = np.bincount(g.counters, minlength=64)
@@ -31,10 +41,13 @@ def assert_layout_equals_oracle(oracle, pts, res, **gridkw):
     return g
 
 
+@pytest.mark.parametrize("grid", [{}, REFERENCE_GRID], ids=["fast_grid", "reference_grid"])
 @pytest.mark.parametrize("K", [1, 8, 13, 20, 32, 50, 100, 200, 256])
-def test_pts20k_rows_bit_exact(kn, oracle, pts20k, K):
-    res = run_engine(kn, pts20k, K)
-    g = assert_layout_equals_oracle(oracle, pts20k, res)
+def test_pts20k_rows_bit_exact(kn, oracle, pts20k, K, grid):
+    res = run_engine(kn, pts20k, K, **grid)
+    g = assert_layout_equals_oracle(oracle, pts20k, res, **grid)
+    if grid:
+        assert g.dim == 19  # the reference's grid for its own fixture
     assert np.array_equal(res["knn"], g.knn_exact(K))
 
 
@@ -46,17 +59,20 @@ def test_pts20k_sets_match_reference_kdtree_golden(kn, oracle, pts20k, K):
     golden = np.load(GOLDEN / f"pts20k_kdtree_k{K}_rowhash.npy")
     mism = np.nonzero(set_hash(idx) != golden)[0]
     # the only rows that may differ are the fixture's exact k/k+1 ties, checked row by row on the oracle
-    g = oracle.Grid(pts20k)
+    g = default_grid(oracle, pts20k, K)
     assert np.array_equal(res["knn"], g.knn_exact(K))
     assert len(mism) == assert_sets_match_golden_hash(oracle, pts20k, g, K, golden)
 
 
 @pytest.mark.parametrize("n,K,seed", [(11545, 50, 1), (100_000, 20, 2), (300_000, 50, 20171004),
                                       (1_000_000, 20, 20171004), (1_000_000, 8, 1), (500_000, 32, 2)])
-def test_uniform_rows_bit_exact(kn, oracle, n, K, seed):
+@pytest.mark.parametrize("grid", [{}, REFERENCE_GRID, {"algorithm": 4}], ids=["fast_grid", "reference_grid", "fast_grid_no_tile"])
+def test_uniform_rows_bit_exact(kn, oracle, n, K, seed, grid):
+    """fast_grid: the default grid, tile kernel (+ select kernel for blocks it hands over, + retry kernel);
+    reference_grid: the reference's cube, select kernel; fast_grid_no_tile: the default grid without the tile kernel."""
     pts = oracle.generate_uniform(n, seed=seed)
-    res = run_engine(kn, pts, K)
-    g = assert_layout_equals_oracle(oracle, pts, res)
+    res = run_engine(kn, pts, K, **grid)
+    g = assert_layout_equals_oracle(oracle, pts, res, **{k: v for k, v in grid.items() if k != "algorithm"})
     assert np.array_equal(res["knn"], g.knn_exact(K))
     if n >= 1_000_000:  # restarts are a cost, not an error; smaller clouds are mostly domain boundary
         assert res["timings"]["restarts"] < n // 20
@@ -78,12 +94,12 @@ def test_general_kernel_alone_gives_the_same_rows(kn, oracle, K):
     a = run_engine(kn, pts, K)
     b = run_engine(kn, pts, K, algorithm=1)
     assert np.array_equal(a["knn"], b["knn"])
-    assert np.array_equal(a["knn"], oracle.Grid(pts).knn_exact(K))
+    assert np.array_equal(a["knn"], default_grid(oracle, pts, K).knn_exact(K))
 
 
 def test_search_radius_guess_does_not_change_rows(kn, oracle):
     pts = oracle.generate_uniform(150_000, seed=14)
-    want = oracle.Grid(pts).knn_exact(20)
+    want = default_grid(oracle, pts, 20).knn_exact(20)
     for scale in (0.3, 0.7, 1.0, 1.6, 3.0, 6.0):  # tiny guess: everything retried; huge: beyond the row table
         r = run_engine(kn, pts, 20, search_scale=scale)
         assert np.array_equal(r["knn"], want), scale
@@ -146,7 +162,7 @@ def test_distances_and_external_query_points(kn, oracle):
     """distances of the rows, and queries that are not data points (what the reference's kd-tree
     offers, kd_tree.cpp:168-192).  Distances are bit-exact (same f32 expression), rows are exact."""
     pts = oracle.generate_uniform(80_000, seed=17)
-    g = oracle.Grid(pts)
+    g = default_grid(oracle, pts, 20)
     rng = np.random.default_rng(5)
     with kn.KnProblem(pts, k=20) as p:
         p.solve()
@@ -163,9 +179,9 @@ def test_distances_and_external_query_points(kn, oracle):
         assert np.array_equal(got, want)
         assert np.array_equal(got_d2.view(np.uint32), want_q_d2.view(np.uint32))
         assert (got[3200:3300, 0] == np.arange(200, 300)).all()  # a query on a data point finds it at distance 0
-    with kn.KnProblem(pts, k=50) as p:  # works before knc_solve too
+    with kn.KnProblem(pts, k=50) as p:  # works before knc_solve too (another k: another default grid, other positions)
         q = rng.random((500, 3)).astype(np.float32) * 1000
-        assert np.array_equal(p.query_points(q), oracle.brute_external(g.sorted_xyz, q, 50))
+        assert np.array_equal(p.query_points(q), oracle.brute_external(p.get_points(), q, 50))
 
 
 def test_original_space_remap(kn, oracle):
@@ -189,7 +205,7 @@ def test_single_point_and_fewer_points_than_k(kn, oracle):
     assert r["knn"].shape == (1, 8) and (r["knn"] == kn.EMPTY).all()
     pts = oracle.generate_uniform(7, seed=3)
     r = run_engine(kn, pts, 20)
-    g = oracle.Grid(pts)
+    g = default_grid(oracle, pts, 20)
     assert np.array_equal(r["knn"], g.knn_exact(20))
     assert (r["knn"][:, 6:] == kn.EMPTY).all() and (r["knn"][:, :6] != kn.EMPTY).all()
 
@@ -226,7 +242,7 @@ def test_presorted_and_repeated_input_takes_the_aggregated_atomics(kn, oracle):
     """Input that is already in cell order (every warp of the count kernel sees runs of equal cells: the
     warp-aggregated atomic path) and input with long runs of one repeated point."""
     base = oracle.generate_uniform(120_000, seed=23)
-    g0 = oracle.Grid(base)
+    g0 = default_grid(oracle, base, 8)
     for pts in (np.ascontiguousarray(g0.sorted_xyz),                      # cell-ordered input
                 np.ascontiguousarray(np.repeat(base[:3000], 40, axis=0))):  # 40 copies of each point, adjacent
         r = run_engine(kn, pts, 8)
@@ -281,20 +297,27 @@ def test_slab_mode_rows_equal_whole_grid_rows(kn, oracle):
     whole-grid rows, shifted by the slab's first sorted position."""
     pts = oracle.generate_uniform(400_000, seed=20171004)
     K = 20
-    g = oracle.Grid(pts)
-    D = g.dim
+    for dims, slabs in [((51, 51, 51), [(0, 14, 0, 10), (6, 30, 10, 26), (35, 51, 39, 51)]),   # the reference's cube
+                        (oracle.fast_dims(len(pts), K), [(0, 9, 0, 6), (4, 20, 7, 17), (26, 36, 29, 36)])]:
+        _check_slabs(kn, oracle, pts, K, dims, slabs)
+
+
+def _check_slabs(kn, oracle, pts, K, dims, slabs):
+    g = oracle.Grid(pts, dims=dims)
+    D, plane = dims[2], dims[0] * dims[1]
+    assert slabs[-1][1] == D
     full = g.knn_exact(K)
     cz = np.clip(np.floor(pts[:, 2] * np.float32(D) / np.float32(1000)).astype(int), 0, D - 1)
-    for (zb, ze, ozb, oze) in [(0, 14, 0, 10), (6, 30, 10, 26), (D - 16, D, D - 12, D)]:
+    for (zb, ze, ozb, oze) in slabs:
         keep = (cz >= zb) & (cz < ze)
         sub = np.ascontiguousarray(pts[keep])
-        with kn.KnProblem(sub, k=K, grid_dim=D, slab=(zb, ze, ozb, oze)) as p:
+        with kn.KnProblem(sub, k=K, grid_dims=dims, slab=(zb, ze, ozb, oze)) as p:
             p.solve()
             rows, perm, info = p.get_knearests(), p.get_permutation(), p.info
-        # global sorted positions of the slab: contiguous, starting at ptrs[zb * D * D]
-        base = int(g.ptrs[zb * D * D])
-        q0 = int(g.ptrs[ozb * D * D]) - base
-        q1 = int(g.ptrs[oze * D * D]) - base
+        # global sorted positions of the slab: contiguous, starting at ptrs[zb * plane]
+        base = int(g.ptrs[zb * plane])
+        q0 = int(g.ptrs[ozb * plane]) - base
+        q1 = int(g.ptrs[oze * plane]) - base
         assert (info.query_begin, info.query_count) == (q0, q1 - q0)
         want = full[base + q0: base + q1].astype(np.int64) - base
         assert np.array_equal(rows.astype(np.int64), want)
@@ -351,7 +374,7 @@ def test_ten_million_points_properties_and_sampled_brute_force(kn, oracle):
         knn = p.get_knearests()
         perm = p.get_permutation()
         pts = p.get_points()
-        assert p.info.dimx == 148
+        assert (p.info.dimx, p.info.dimy, p.info.dimz) == oracle.fast_dims(n, K)
     # permutation is a bijection (test_knearests.cu:162-168)
     seen = np.zeros(n, np.uint8)
     seen[perm] = 1

@@ -12,23 +12,28 @@ import pytest
 pytestmark = pytest.mark.gpu
 
 
-def canonical_pair(oracle, kn, pts, K):
+def canonical_pair(oracle, kn, pts, K, **grid):
+    """Ours on the library's own grid unless `grid` names another: the comparison is in original indices, so the
+    two sides need not share a grid."""
     if not oracle.have_ref(f"libref_knearests_k{K}.so"):
         pytest.skip("oracle/_ref not built")
     ref = oracle.RefGpu(K).run(pts)
-    with kn.KnProblem(pts, k=K) as p:
+    with kn.KnProblem(pts, k=K, **grid) as p:
         p.solve()
         mine = {"knn": p.get_knearests(), "perm": p.get_permutation(), "dim": p.info.dimx}
-    assert ref["dim"] == mine["dim"]  # same grid sizing, knearests.cu:249
+    assert ref["dim"] == kn.grid_dim(len(pts), 3.1)  # same grid sizing rule, knearests.cu:249
+    if grid:
+        assert ref["dim"] == mine["dim"]
     assert np.array_equal(np.sort(ref["permutation"]), np.arange(len(pts), dtype=np.uint32))
     ia, da = oracle.canonical_rows(mine["knn"], mine["perm"], pts)
     ib, db = oracle.canonical_rows(ref["knn"], ref["permutation"], pts)
     return ia, da, ib, db
 
 
+@pytest.mark.parametrize("grid", [{}, {"density": 3.1}], ids=["fast_grid", "reference_grid"])
 @pytest.mark.parametrize("K", [8, 20, 32, 50])
-def test_pts20k_against_reference_gpu(kn, oracle, pts20k, K):
-    ia, da, ib, db = canonical_pair(oracle, kn, pts20k, K)
+def test_pts20k_against_reference_gpu(kn, oracle, pts20k, K, grid):
+    ia, da, ib, db = canonical_pair(oracle, kn, pts20k, K, **grid)
     same, ties, bad = oracle.compare_canonical(ia, da, ib, db, ulp_slack=0)
     assert bad == [] and same + ties == len(pts20k)
     assert np.array_equal(da, db) or ties > 0  # same distances, bit for bit, wherever the sets agree

@@ -39,15 +39,15 @@ def test_random_clouds_match_the_oracle(kn, oracle, seed):
         kind = KINDS[(seed + case) % len(KINDS)]
         n = int(rng.choice([1, 2, 3, 17, 100, 999, 5000, 20000, 60000]))
         k = int(rng.choice([1, 2, 8, 13, 20, 32, 50, 64, 100]))
-        density = float(rng.choice([0.0, 0.5, 1.0, 3.1, 10.0]))
-        alg = int(rng.choice([0, 0, 0, 1, 2]))
+        density = float(rng.choice([0.0, 0.0, 0.5, 1.0, 3.1, 10.0]))  # 0: the library's own (non-cubic) grid
+        alg = int(rng.choice([0, 0, 0, 1, 2, 4]))
         pts = np.ascontiguousarray(make_cloud(rng, kind, n), np.float32)
         tag = f"seed={seed} case={case} kind={kind} n={n} k={k} density={density} algorithm={alg}"
         with kn.KnProblem(pts, k=k, density=density, algorithm=alg) as p:
             p.solve()
             rows, perm, spts = p.get_knearests(), p.get_permutation(), p.get_points()
             d2 = p.get_dists()
-        g = oracle.Grid(pts, density=density if density > 0 else 3.1)
+        g = oracle.Grid(pts, density=density) if density > 0 else oracle.Grid(pts, dims=oracle.fast_dims(n, k))
         assert np.array_equal(perm, g.permutation), tag
         assert np.array_equal(spts, g.sorted_xyz), tag
         want, want_d2 = g.knn_exact(k, with_d2=True)
@@ -68,12 +68,13 @@ def test_random_slabs_external_queries_and_streaming(kn, oracle, seed):
         k = int(rng.choice([8, 20, 32]))
         pts = np.ascontiguousarray(make_cloud(rng, kind, n), np.float32)
         tag = f"seed={seed} case={case} kind={kind} n={n} k={k}"
-        g = oracle.Grid(pts)
-        D = g.dim
+        dims = oracle.fast_dims(n, k) if case % 2 else (oracle.grid_dim(n),) * 3
+        g = oracle.Grid(pts, dims=dims)
+        D, plane = dims[2], dims[0] * dims[1]
         full = g.knn_exact(k)
         # streamed solve == plain solve == oracle
         pinned = torch.empty(full.shape, dtype=torch.int32, pin_memory=True)
-        with kn.KnProblem(pts, k=k) as p:
+        with kn.KnProblem(pts, k=k, grid_dims=dims) as p:
             got = p.solve_to_host(pinned.numpy().view(np.uint32), chunks=int(rng.integers(1, 9)))
             assert np.array_equal(got, full), tag
             q = np.ascontiguousarray(make_cloud(rng, "out_of_range", 300), np.float32)
@@ -84,14 +85,14 @@ def test_random_slabs_external_queries_and_streaming(kn, oracle, seed):
         ozb = int(rng.integers(0, D - 2))
         oze = int(rng.integers(ozb + 1, D + 1))
         cz = np.clip(np.floor(pts[:, 2] * np.float32(D) / np.float32(1000)).astype(int), 0, D - 1)
-        for halo in (slabs.halo_planes(k), D):  # the driver's halo may be too thin for odd clouds: then it must say so
+        for halo in (slabs.halo_planes(k, n, D), D):  # the driver's halo may be too thin for odd clouds: then it must say so
             zb, ze = max(0, ozb - halo), min(D, oze + halo)
             sub = np.ascontiguousarray(pts[(cz >= zb) & (cz < ze)])
             if len(sub) == 0:
                 break
-            base = int(g.ptrs[zb * D * D])
-            q0, q1 = int(g.ptrs[ozb * D * D]) - base, int(g.ptrs[oze * D * D]) - base
-            with kn.KnProblem(sub, k=k, grid_dim=D, slab=(zb, ze, ozb, oze)) as p:
+            base = int(g.ptrs[zb * plane])
+            q0, q1 = int(g.ptrs[ozb * plane]) - base, int(g.ptrs[oze * plane]) - base
+            with kn.KnProblem(sub, k=k, grid_dims=dims, slab=(zb, ze, ozb, oze)) as p:
                 try:
                     p.solve()
                 except kn.KnError as e:
