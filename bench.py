@@ -385,7 +385,7 @@ def main_ours(args, rank: int, world: int, local_rank: int):
             "roofline": roofline, "cpu_baseline": cpu_baseline,
             "device_ms": {"grid_build": build_ms, "query": solve_ms},
             "solve_only_value": n / (solve_ms * 1e-3), "reference_gpu": reference_gpu, "verify": verify,
-            "restarts": int(timings[-1]["restarts"])}
+            "restarts": int(timings[-1]["restarts"]), "handed_over_blocks": int(timings[-1]["handed_over_blocks"])}
     print(json.dumps(line), flush=True)
 
 

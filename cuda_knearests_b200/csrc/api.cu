@@ -396,6 +396,7 @@ static int solve_impl(knc_problem *p, unsigned int *out_knn_host, int chunks, co
     if (out_knn_host) CU(cudaStreamSynchronize(p->copy_stream));
     CU(cudaEventElapsedTime(&p->t.solve_ms, p->ev[2], p->ev[3]));
     p->t.restarts = diag[0];  // restarts inside the general kernel + queries it took over from the fast one
+    p->t.handed_over_blocks = diag[4];  // last chunk's (the counter restarts with every chunk)
     memcpy(&p->t.max_radius2, &diag[1], sizeof(float));
     p->solved = 1;
     if (verbose()) {

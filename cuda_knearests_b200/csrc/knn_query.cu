@@ -611,11 +611,17 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
 // sets up segment L (two pointer loads, a warp prefix sum for the place in the tile) and issues its copy.
 //
 // While the copies fly every lane works out its own windows ("spans") of those rows as before, in global
-// positions, then rebases them to tile slots.  The scan needs NO bounds test and no predicated load: a span that
-// ends inside a segment is followed by records of the same row that lie beyond the sphere's reach in x (they fail
-// the distance test like any other), a segment is followed by kTilePad records of +inf, and a lane that has run
-// out of spans parks on four +inf records at slot 0 -- so the body is 4 x LDS.128, the arithmetic, and a predicated
-// 16-bit append of the tile slot.  Selection as in the select kernel, keys rebuilt from the tile; the neighbour's
+// positions, then rebases them to tile slots.  The scan needs NO bounds test and no predicated load: a span
+// lies inside a segment, between records of the same row that are beyond the sphere's reach in x (they fail the
+// distance test like any other); a segment lies between runs of kTilePad records of +inf; and a lane that has run
+// out of spans parks on +inf records at the head of the tile -- so the body is 4 x LDS.128, the arithmetic, and a
+// predicated 16-bit append of the tile slot.
+//
+// Bank conflicts: 32 lanes reading 32 unrelated 16-byte records cost ~8.3 shared-memory wavefronts per LDS.128
+// where 4 is the minimum (profiles/r2_notes.md), and the shared-memory pipe is what bounds this kernel.  So every
+// lane starts a span up to 7 records EARLY, on a slot that is congruent to (lane + 4 x iteration) modulo 8: the
+// eight lanes of a quarter warp then always touch eight different 16-byte bank groups -- 4 wavefronts, always --
+// at the price of 3.5 extra records per span (records before a span fail the distance test like those after it).  Selection as in the select kernel, keys rebuilt from the tile; the neighbour's
 // sorted position is the 4th word of its record.  The block's rows are laid out in shared memory exactly as in
 // global memory and leave as ONE bulk copy.
 //
@@ -623,7 +629,8 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
 // itself in P.block_list and is served by the select kernel afterwards.
 constexpr int kTileQueryRows = 3;
 constexpr int kTileSegs = 9 * kTileQueryRows;  // <= 32: one lane of warp 0 each
-constexpr int kTilePad = 4;                    // +inf records after every segment and at slots 0..3
+constexpr int kTilePad = 8;                    // +inf records after every segment: 3 read past a span's end, 7 before the next
+constexpr int kTileHead = 16;                  // +inf records at the head of the tile: where lanes without work park
 
 __device__ __forceinline__ unsigned smem_addr(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 
@@ -653,54 +660,81 @@ __device__ __forceinline__ void bulk_store(void *dst, unsigned src, unsigned byt
 __device__ __forceinline__ void bulk_store_wait() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// {c.x - px, c.y - py} in ONE instruction (FADD2 on sm_100a): the record's x, y and the query's x, y each sit in an
+// aligned register pair.  IEEE per component, so the differences are the reference's (knearests.cu:125).
+__device__ __forceinline__ float2 sub2(float ax, float ay, unsigned long long pxy) {
+    unsigned long long a, r;
+    float2 d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(ax), "f"(ay));
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(pxy));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(r));
+    return d;
+}
+__device__ __forceinline__ float2 sq2(float2 v) {  // {v.x * v.x, v.y * v.y}, each rounded (FMUL2)
+    unsigned long long a, r;
+    float2 d;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(a) : "f"(v.x), "f"(v.y));
+    asm("mul.rn.f32x2 %0, %1, %1;" : "=l"(r) : "l"(a));
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(d.x), "=f"(d.y) : "l"(r));
+    return d;
+}
+
 template <int K_T, int QB, int NET, int CAP, int TCAP>
 __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant__ QueryParams P) {
     static_assert(K_T > 0 && K_T + 1 <= NET - 8, "tile path: k must leave room for new keys in a round");
     static_assert(NET == 32 || NET == 64, "tile path: networks exist for 32 and 64 keys");
     static_assert(TCAP < 65536 && TCAP % 8 == 0, "tile slots are stored in 16 bits");
-    static_assert((size_t)TCAP * 16 + (size_t)CAP * QB * 2 >= (size_t)QB * K_T * 4, "row staging reuses tile + buffer");
     constexpr unsigned kSlotMask = CAP <= 64 ? 63u : 127u;  // low key bits that hold the buffer slot
     constexpr int kSlotBits = CAP <= 64 ? 6 : 7;
     static_assert(CAP <= 128, "slot must fit the low key bits");
+    // Shared memory: the tile, then one PRIVATE region per warp: candidate buffer [CAP][32] of 16-bit tile slots,
+    // span list [10][32].  Private, so that a warp that is done can stage its rows there without a block barrier.
+    constexpr int kBufBytes = CAP * 64, kSpanBytes = 10 * 128, kWarpBytes = kBufBytes + kSpanBytes;
+    static_assert(kWarpBytes >= 32 * K_T * 4, "a warp's rows are staged in its own buffer + span area");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) unsigned long long s_bar;
     __shared__ int s_adj[32];      // per segment: tile slot = s_adj + global sorted position
-    __shared__ int s_ends[4];      // query row and x cell of the block's first and last query
+    __shared__ int s_ends[4];      // [0]: query row of the block's first query
     __shared__ int s_fallback;
-    const int tid = threadIdx.x, lane = tid & 31;
-    float4 *tile = reinterpret_cast<float4 *>(smem_raw);                                           // [TCAP] records
-    unsigned short *BUF = reinterpret_cast<unsigned short *>(smem_raw + (size_t)TCAP * 16) + tid;   // [CAP][QB] tile slots
-    unsigned *SP = reinterpret_cast<unsigned *>(smem_raw + (size_t)TCAP * 16 + (size_t)CAP * QB * 2) + tid;  // [10][QB] spans
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    float4 *tile = reinterpret_cast<float4 *>(smem_raw);                                  // [TCAP] records
+    unsigned char *mine = smem_raw + (size_t)TCAP * 16 + (size_t)warp * kWarpBytes;          // this warp's region
+    unsigned short *BUF = reinterpret_cast<unsigned short *>(mine) + lane;                   // [CAP][32] tile slots
+    unsigned *SP = reinterpret_cast<unsigned *>(mine + kBufBytes) + lane;                    // [10][32] spans
     const int Dx = P.g.Dx, Dy = P.g.Dy, zb = P.g.zb, ze = P.g.ze;
     const long long row0 = (long long)blockIdx.x * QB;
     const int rows = (int)min((long long)QB, (long long)P.query_count - row0);
     const bool valid = tid < rows;
     const int q = P.query_begin + (int)row0 + min(tid, rows - 1);
     const QueryGeom s = query_geom(__ldg(P.pts + q), P.g);
-    const int ci = max(0, min(Dx - 1, (int)floorf(s.tx)));  // the build's cell (same arithmetic, knearests.cu:23-28)
     const int qrow = (s.ck - zb) * Dy + s.cj;
     const unsigned bar = smem_addr(&s_bar);
-    if (tid == 0) { mbar_init(bar, 1); s_ends[0] = qrow; s_ends[1] = ci; }
-    if (tid == rows - 1) { s_ends[2] = qrow; s_ends[3] = ci; }
-    __syncthreads();
-    const int qrow0 = s_ends[0], nqr = s_ends[2] - qrow0 + 1;
     const float4 inf4 = make_float4(__int_as_float(0x7f800000), __int_as_float(0x7f800000), __int_as_float(0x7f800000), 0.f);
 
-    // ---- warp 0: the segments.  Lane = (query row qi, candidate row dj, dk) ------------------------------------
+    // ---- warp 0: the segments.  Lane = (query row qi, candidate row dj, dk).  It looks at the block's first and last
+    // query itself (two broadcast loads), so nobody waits for anybody before the copies are on their way. ----------
     if (tid < 32) {
+        if (tid == 0) mbar_init(bar, 1);
+        const QueryGeom sf = query_geom(__ldg(P.pts + P.query_begin + (int)row0), P.g);
+        const QueryGeom sl = query_geom(__ldg(P.pts + P.query_begin + (int)row0 + rows - 1), P.g);
+        const int cif = max(0, min(Dx - 1, (int)floorf(sf.tx)));  // the build's cells (same arithmetic, knearests.cu:23-28)
+        const int cil = max(0, min(Dx - 1, (int)floorf(sl.tx)));
+        const int qrow0 = (sf.ck - zb) * Dy + sf.cj, nqr = (sl.ck - zb) * Dy + sl.cj - qrow0 + 1;
+        __syncwarp();  // the barrier is initialised before any lane uses it
         int len = 0, g0 = 0;
         const bool rows_ok = nqr <= kTileQueryRows;
         if (rows_ok && lane < nqr * 9) {
             const int qi = lane / 9, rr = lane - 9 * qi, dj = rr % 3 - 1, dk = rr / 3 - 1;
             const int R = qrow0 + qi, j = R % Dy + dj, k = R / Dy + zb + dk;
             if (j >= 0 && j < Dy && k >= zb && k < ze) {
-                const int xlo = qi == 0 ? s_ends[1] : 0, xhi = qi == nqr - 1 ? s_ends[3] : Dx - 1;
+                const int xlo = qi == 0 ? cif : 0, xhi = qi == nqr - 1 ? cil : Dx - 1;
                 const int xa = max(0, xlo - P.halo_cells), xb = min(Dx - 1, xhi + P.halo_cells);
                 const int base = ((k - zb) * Dy + j) * Dx;
                 g0 = __ldg(P.ptrs + base + xa);
                 len = __ldg(P.ptrs + base + xb + 1) - g0;
             }
         }
+        if (lane == 0) s_ends[0] = qrow0;
         const int need = len > 0 ? len + kTilePad : 0;
         int incl = need, bytes = len * 16;
 #pragma unroll
@@ -710,20 +744,18 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
         }
 #pragma unroll
         for (int d = 16; d > 0; d >>= 1) bytes += __shfl_xor_sync(0xffffffffu, bytes, d);
-        const int total = __shfl_sync(0xffffffffu, incl, 31) + kTilePad;
-        const int off = kTilePad + incl - need;  // slots 0..3: the parking records
+        const int total = __shfl_sync(0xffffffffu, incl, 31) + kTileHead;
+        const int off = kTileHead + incl - need;
         const bool ok = rows_ok && total <= TCAP;
         if (ok) {
             s_adj[lane] = off - g0;
+            if (lane == 0) mbar_arrive_expect_tx(bar, (unsigned)bytes);  // the one arrival of the phase, with the byte
+            __syncwarp();                                                // count of all copies, before any of them
+            if (lane < kTileHead) tile[lane] = inf4;
             if (len > 0) {
                 bulk_load(smem_addr(tile + off), P.pts + g0, (unsigned)len * 16u, bar);
 #pragma unroll
                 for (int u = 0; u < kTilePad; ++u) tile[off + len + u] = inf4;
-            }
-            if (lane == 0) {
-#pragma unroll
-                for (int u = 0; u < kTilePad; ++u) tile[u] = inf4;
-                mbar_arrive_expect_tx(bar, (unsigned)bytes);
             }
         }
         if (lane == 0) s_fallback = ok ? 0 : 1;
@@ -748,75 +780,131 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
             }
         }
     }
-    __syncthreads();
+    __syncthreads();  // the only block-wide barrier: the segment table (and the mbarrier) are ready
     if (s_fallback) {  // block-uniform
         if (tid == 0) P.block_list[atomicAdd(P.block_count, 1u)] = (int)blockIdx.x;
         return;
     }
-    const int qi = qrow - qrow0;
+    const int qi = qrow - s_ends[0];
     int nsp = 0;
 #pragma unroll
     for (int rr = 0; rr < 9; ++rr)
         if (ge[rr] > gb[rr]) {
             const int adj = s_adj[qi * 9 + rr];
-            SP[nsp * QB] = (unsigned)(gb[rr] + adj) | ((unsigned)(ge[rr] + adj) << 16);
+            SP[nsp * 32] = (unsigned)(gb[rr] + adj) | ((unsigned)(ge[rr] + adj) << 16);
             ++nsp;
         }
-    SP[nsp * QB] = 0u;  // terminator: the parking records at slot 0, recognised by end == 0
+    SP[nsp * 32] = 8u;  // terminator: begin 8 (parks inside the head of the tile), end 0 -- recognised by end == 0
     const int my_slot = q + s_adj[qi * 9 + 4];
 
     // Append pointer (shared-memory address of the lane's next free buffer entry), clamped once per chunk: a chunk
     // may run kSelChunk entries past `wlim`, reaching wlim at all counts as an overflow.
     const unsigned wp0 = smem_addr(BUF);
-    const unsigned wlim = wp0 + (unsigned)(CAP - kSelChunk) * QB * 2u;
+    const unsigned wlim = wp0 + (unsigned)(CAP - kSelChunk) * 64u;
     unsigned wp = wp0;
 
     while (!mbar_try_wait(bar, 0)) {}  // the tile has landed
 
-    // ---- scan: lock step over the lanes' own span lists, kSelChunk records per iteration --------------------------
+    // ---- scan: lock step over the lanes' own span lists, kSelChunk records per iteration, software-pipelined: the
+    // records of the NEXT chunk are requested before the current one is evaluated.  The test here is a PREFILTER
+    // (packed arithmetic: {dx, dy} and their squares in one instruction each; the sum is within 2 ulp of the
+    // reference's expression, the radius is widened by 2^-20 to cover it): whatever passes gets its exact distance
+    // when the keys are built, and the row is accepted only if its k-th exact distance lies inside the true sphere.
     {
+        static_assert(kSelChunk == 4, "the conflict-free start below assumes chunks of 4 records");
+        const float r2a = r2 * (1.0f + 1.0f / 1048576.0f);
+        unsigned long long pxy;
+        asm("mov.b64 %0, {%1, %2};" : "=l"(pxy) : "f"(s.px), "f"(s.py));
+        int ph = lane;  // slot residue (mod 8) this lane must read at in the coming iteration: lane + 4 x (iteration & 1)
         const unsigned t0 = SP[0];
-        int ts = (int)(t0 & 0xffffu), end = (int)(t0 >> 16), sp = min(1, nsp);
-        do {
-            float4 c[kSelChunk];
+        int end = (int)(t0 >> 16);
+        int ts = (int)(t0 & 0xffffu);
+        ts -= (ts - ph) & 7;
+        const unsigned spterm = smem_addr(SP + nsp * 32);         // the terminator entry
+        unsigned spaddr = min(smem_addr(SP + 32), spterm);        // the entry the next switch reads
+        auto fetch = [&](float4(&c)[kSelChunk], int at) {
 #pragma unroll
-            for (int u = 0; u < kSelChunk; ++u) c[u] = tile[ts + u];
+            for (int u = 0; u < kSelChunk; ++u) c[u] = tile[at + u];
+        };
+        auto evaluate = [&](const float4(&c)[kSelChunk], int at) {
 #pragma unroll
             for (int u = 0; u < kSelChunk; ++u) {
-                const float dx = c[u].x - s.px, dy = c[u].y - s.py, dz = c[u].z - s.pz;
-                const float d2 = __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+                const float2 q2 = sq2(sub2(c[u].x, c[u].y, pxy));
+                const float dz = c[u].z - s.pz;
+                const float d2 = __fmaf_rn(dz, dz, __fadd_rn(q2.x, q2.y));
                 asm volatile("{\n\t.reg .pred p;\n\tsetp.le.f32 p, %1, %2;\n\t"
-                             "@p st.shared.u16 [%0], %3;\n\t@p add.u32 %0, %0, %4;\n\t}"
+                             "@p st.shared.u16 [%0], %3;\n\t@p add.u32 %0, %0, 64;\n\t}"
                              : "+r"(wp)
-                             : "f"(d2), "f"(r2), "r"(ts + u), "n"(QB * 2));
+                             : "f"(d2), "f"(r2a), "r"(at + u));
             }
             wp = min(wp, wlim);
-            ts += kSelChunk;
-            if (ts >= end) {
-                const unsigned t = SP[sp * QB];
-                ts = (int)(t & 0xffffu); end = (int)(t >> 16);
-                sp = min(sp + 1, nsp);
-            }
-        } while (__any_sync(0xffffffffu, end != 0));
+        };
+        // One step along the lane's span list, straight-line predicated code (the compiler made a divergent branch
+        // of it): the next chunk of the span, or -- past its end -- the first chunk of the next span, started on the
+        // slot residue of the coming iteration.
+        auto advance = [&]() {
+            asm volatile("{\n\t.reg .pred p;\n\t.reg .u32 t, b;\n\t"
+                         "add.s32 %0, %0, 4;\n\t"
+                         "xor.b32 %3, %3, 4;\n\t"
+                         "setp.ge.s32 p, %0, %1;\n\t"
+                         "@p ld.shared.u32 t, [%2];\n\t"
+                         "@p shr.u32 %1, t, 16;\n\t"
+                         "@p and.b32 b, t, 0xffff;\n\t"
+                         "@p sub.s32 t, b, %3;\n\t"
+                         "@p and.b32 t, t, 7;\n\t"
+                         "@p sub.s32 %0, b, t;\n\t"
+                         "@p add.u32 %2, %2, 128;\n\t"
+                         "@p min.u32 %2, %2, %4;\n\t}"
+                         : "+r"(ts), "+r"(end), "+r"(spaddr), "+r"(ph)
+                         : "r"(spterm)
+                         : "memory");
+        };
+        float4 ca[kSelChunk], cb[kSelChunk];
+        fetch(ca, ts);
+        while (true) {
+            int tc = ts;
+            advance();
+            fetch(cb, ts);
+            evaluate(ca, tc);
+            if (!__any_sync(0xffffffffu, end != 0)) break;
+            tc = ts;
+            advance();
+            fetch(ca, ts);
+            evaluate(cb, tc);
+            if (!__any_sync(0xffffffffu, end != 0)) break;
+        }
     }
 
     // ---- select (see kn_query_select_kernel): 32-bit keys = bits(d2) with the low bits replaced by the buffer slot ----
     asm volatile("" ::: "memory");  // the appends above were written behind the compiler's back
-    const int cnt = (int)((wp - wp0) / (QB * 2u)) - 1;  // candidates inside the sphere, the query itself not counted
+    const int cnt = (int)((wp - wp0) / 64u) - 1;  // candidates that passed the prefilter, the query itself not counted
     const bool searched = valid && cnt >= K_T && wp < wlim;
     const int have = searched ? cnt + 1 : 0;
     unsigned a[NET];
     for (int base = 0, round = 0; round == 0 || __any_sync(0xffffffffu, have > base); ++round) {
+        // Keys of the next NET - lo buffered candidates, eight at a time and without branches (all slot reads, then all
+        // record reads, then the arithmetic: the loads of a group overlap).  A slot beyond `have` reads the +inf record
+        // at the head of the tile and becomes the largest key.
         const int lo = round == 0 ? 0 : K_T + 1;
 #pragma unroll
-        for (int u = 0; u < NET; ++u) {
-            if (u >= lo) {
-                const int slot = base + (u - lo);
-                a[u] = 0xFFFFFFFFu;
-                if (slot < have) {
-                    const int ti = (int)BUF[slot * QB];
-                    const unsigned key = ((unsigned)(make_key(tile[ti], s, 0) >> 32) & ~kSlotMask) | (unsigned)slot;
-                    a[u] = ti == my_slot ? 0xFFFFFFFFu : key;  // self excluded by position, knearests.cu:123
+        for (int g = 0; g < NET; g += 8) {
+            if (g + 8 > lo) {
+                int ti[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const int slot = base + (g + j - lo);
+                    ti[j] = (g + j >= lo && slot < have) ? (int)BUF[slot * 32] : 0;
+                }
+                float4 rec[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) rec[j] = tile[ti[j]];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    if (g + j >= lo) {
+                        const int slot = base + (g + j - lo);
+                        const unsigned key = ((unsigned)(make_key(rec[j], s, 0) >> 32) & ~kSlotMask) | (unsigned)slot;
+                        a[g + j] = (slot < have && ti[j] != my_slot) ? key : 0xFFFFFFFFu;  // self excluded, knearests.cu:123
+                    }
                 }
             }
         }
@@ -830,42 +918,47 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
         if constexpr (NET == 32) { KN_SORT_NETWORK_32(KN_CE) } else { KN_SORT_NETWORK_64(KN_CE) }
 #undef KN_CE
     }
-    bool exact = searched;
+    // exact: k strictly increasing truncated distances, and the k-th inside the TRUE sphere (the prefilter's is wider)
+    const bool inside = (a[K_T - 1] | kSlotMask) <= __float_as_uint(r2);
+    bool exact = searched && inside;
 #pragma unroll
     for (int u = 0; u < K_T; ++u) exact = exact && (a[u] >> kSlotBits) < (a[u + 1] >> kSlotBits);
-    if (valid && !exact) P.retry_list[atomicAdd(P.retry_count, 1u)] = q | (cnt < K_T ? (int)0x80000000 : 0);
+    if (valid && !exact)
+        P.retry_list[atomicAdd(P.retry_count, 1u)] = q | ((cnt < K_T || (searched && !inside)) ? (int)0x80000000 : 0);
     report_diag(P, s, exact, exact ? __uint_as_float((a[K_T - 1] | kSlotMask)) : 0.f, 0u, tid);
 
     unsigned res[K_T];
 #pragma unroll
     for (int u = 0; u < K_T; ++u)
-        res[u] = exact ? __float_as_uint(tile[BUF[(a[u] & kSlotMask) * QB]].w) + P.index_offset : KNC_EMPTY;
+        res[u] = exact ? __float_as_uint(tile[BUF[(a[u] & kSlotMask) * 32]].w) + P.index_offset : KNC_EMPTY;
 
-    // ---- rows: staged in shared memory exactly as they lie in global memory, then one bulk copy ----------------------
-    __syncthreads();  // every lane is done reading the tile and the buffer
-    unsigned *OUT = reinterpret_cast<unsigned *>(smem_raw);
+    // ---- rows: every warp stages its 32 rows in its own region, laid out exactly as in global memory, and sends them
+    // off as one bulk copy; no block-wide barrier, a warp that is done is done ------------------------------------------
+    __syncwarp();  // every lane of the warp is done reading the warp's buffer
+    unsigned *OUT = reinterpret_cast<unsigned *>(mine);
     if constexpr (K_T % 4 == 0) {
-        uint4 *dst = reinterpret_cast<uint4 *>(OUT + tid * K_T);
+        uint4 *dst = reinterpret_cast<uint4 *>(OUT + lane * K_T);
 #pragma unroll
         for (int v = 0; v < K_T / 4; ++v) dst[v] = make_uint4(res[4 * v], res[4 * v + 1], res[4 * v + 2], res[4 * v + 3]);
     } else {
         static_assert(K_T % 2 == 0, "row staging writes pairs");
-        uint2 *dst = reinterpret_cast<uint2 *>(OUT + tid * K_T);
+        uint2 *dst = reinterpret_cast<uint2 *>(OUT + lane * K_T);
 #pragma unroll
         for (int v = 0; v < K_T / 2; ++v) dst[v] = make_uint2(res[2 * v], res[2 * v + 1]);
     }
-    unsigned int *out = P.knn + row0 * K_T;
-    const int words = rows * K_T;
-    if (P.bulk_rows_ok && (words & 3) == 0) {  // block-uniform
+    const int wrows = min(32, rows - 32 * warp);  // rows of this warp (<= 0: none)
+    unsigned int *out = P.knn + (row0 + 32 * warp) * K_T;
+    const int words = wrows * K_T;
+    if (P.bulk_rows_ok && (words & 3) == 0) {  // warp-uniform
         fence_async_smem();  // the staged rows must be visible to the copy engine
-        __syncthreads();
-        if (tid == 0) {
+        __syncwarp();
+        if (lane == 0 && words > 0) {
             bulk_store(out, smem_addr(OUT), (unsigned)words * 4u);
             bulk_store_wait();
         }
     } else {
-        __syncthreads();
-        for (int idx = tid; idx < words; idx += QB) out[idx] = OUT[idx];
+        __syncwarp();
+        for (int idx = lane; idx < words; idx += 32) out[idx] = OUT[idx];
     }
 }
 
@@ -1009,9 +1102,11 @@ cudaError_t launch(const QueryParams &P, bool fast, bool tile_ok, cudaStream_t s
             constexpr int NET = K_T <= 20 ? 32 : 64, CAP = K_T <= 20 ? 56 : K_T <= 32 ? 92 : 100;  // 56 and 92: the most that still lets 6 resp. 4 blocks share an SM (228 KB)
             const size_t smem = (sizeof(unsigned) * CAP + sizeof(int2) * kSpanSlots) * QB;
             if (tile_ok) {
-                // tile capacity in records: 9 rows x (QB own + 2 x reach) at one point per cell, + padding, + 4 sigma
-                constexpr int TCAP = K_T <= 8 ? 1472 : K_T <= 20 ? 1536 : K_T <= 32 ? 1600 : 1728;
-                const size_t tsmem = (size_t)TCAP * 16 + (size_t)CAP * QB * 2 + (size_t)10 * QB * 4;
+                // Tile capacity in records: 9 rows x (the x-extent of QB queries + 2 x reach) at ~1 point per cell is
+                // ~1340 at k = 20, + head and padding (~110), + 4 sigma: the x-extent of 128 consecutive queries varies
+                // by sqrt(128) cells and all 9 rows follow it, sigma ~ 107 records (profiles/r2_notes.md).
+                constexpr int TCAP = K_T <= 20 ? 1920 : 2048;
+                const size_t tsmem = (size_t)TCAP * 16 + (size_t)(QB / 32) * ((size_t)CAP * 64 + 10 * 128);
                 e = cudaFuncSetAttribute(kn_query_tile_kernel<K_T, QB, NET, CAP, TCAP>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem);
                 if (e != cudaSuccess) return e;

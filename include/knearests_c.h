@@ -103,6 +103,8 @@ typedef struct {
     float h2d_ms;           /* host->device copy of the input inside knc_prepare (0 for device input)   */
     unsigned int restarts;  /* queries whose first-guess radius was too small (diagnostic)              */
     float max_radius2;      /* largest squared search radius any query ended with                       */
+    unsigned int handed_over_blocks; /* blocks of 128 queries the tile kernel left to the select kernel
+                                        (their candidates did not fit its shared-memory tile; diagnostic)  */
 } knc_timings;
 
 /* ---- the hot path -------------------------------------------------------------------------------- */
