@@ -267,7 +267,7 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     p->dims[0] = dims[0]; p->dims[1] = dims[1]; p->dims[2] = dims[2]; p->cells = cells;
     p->pub.allocated_points = n;
     p->pub.dimx = dims[0]; p->pub.dimy = dims[1]; p->pub.dimz = dims[2];
-    p->pub.num_cell_offsets = 0;
+    p->pub.num_cell_offsets = KN_ROW_TABLE_SIZE;  // rows in the query kernels' (dj, dk) table; the reference: 29 791 cell offsets
 
     // persistent buffers (knearests.cu:313-335, without the `bufsize +=` over-allocation)
     CU(dev_alloc((void **)&p->pub.d_counters, sizeof(int) * (size_t)cells, st));
@@ -320,9 +320,16 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     CU(dev_alloc((void **)&p->pub.d_knearests, sizeof(unsigned) * (size_t)(p->query_count > 0 ? p->query_count : 1) * k, st));
     CU(cudaEventElapsedTime(&p->t.h2d_ms, p->ev[0], p->ev[1]));
     CU(cudaEventElapsedTime(&p->t.build_ms, p->ev[1], p->ev[2]));
-    if (verbose())
+    if (verbose()) {
         fprintf(stderr, "kn_firstbuild: %g msec (n=%d, grid %dx%dx%d planes [%d,%d), k=%d, h2d %g msec)\n",
                 p->t.build_ms, n, dims[0], dims[1], dims[2], zb, ze, k, p->t.h2d_ms);
+        // what the handle keeps on the device (knearests.cu:342 prints its own running total the same way)
+        const size_t held = sizeof(int) * (size_t)(2 * cells + 1) + sizeof(int) + sizeof(float) + sizeof(unsigned) * KN_DIAG_WORDS +
+                            (sizeof(unsigned) + sizeof(float) * 3 + sizeof(float4)) * (size_t)n +
+                            (stride == 4 ? sizeof(unsigned) * (size_t)n : 0) +
+                            sizeof(unsigned) * (size_t)(p->query_count > 0 ? p->query_count : 1) * k;
+        fprintf(stderr, "GPU memory used: %zu Mb\n", held / 1048576);
+    }
 out:
     if (!o.points_on_device && d_in) cudaFreeAsync(d_in, st);
     {
@@ -615,10 +622,20 @@ static void die_on(int rc, const char *where) {
 kn_problem *kn_prepare(float3 *points, int numpoints) {
     knc_problem *p = NULL;
     die_on(knc_prepare((const float *)points, numpoints, 0, &p), "kn_prepare");
+    // printed unconditionally by the reference (knearests.cu:288); here: the rows of the (dj, dk) table that takes
+    // the place of its list of cell offsets
+    fprintf(stderr, "num_cell_offsets = %d\n", p->pub.num_cell_offsets);
     return &p->pub;
 }
 
-void kn_solve(kn_problem *kn) { die_on(knc_solve((knc_problem *)kn), "kn_solve"); }
+void kn_solve(kn_problem *kn) {
+    knc_problem *p = (knc_problem *)kn;
+    die_on(knc_solve(p), "kn_solve");
+    // knearests.cu:389, unconditional there: the farthest ring any query reached / the last ring of the table.  Here a
+    // "ring" is a row of cells in y / z: 1 + the largest final search radius in y/z cell widths, over the table's 5.
+    const double cells_reached = sqrt((double)p->t.max_radius2) / 1000. * (double)(p->dims[1] < p->dims[2] ? p->dims[1] : p->dims[2]) + 1.;
+    fprintf(stderr, "Max visited ring: %g / %g\n", cells_reached, (sqrt((double)p->pub.num_cell_offsets) - 1.) / 2.);
+}
 
 void kn_free(kn_problem **kn) {
     if (!kn || !*kn) return;

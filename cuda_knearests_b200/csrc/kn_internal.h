@@ -32,6 +32,7 @@ struct knc_problem {
 };
 
 #define KN_DIAG_WORDS 8
+#define KN_ROW_TABLE_SIZE 121  // (2 * 5 + 1)^2 rows (dj, dk) around a query's own row: knn_query.cu's table
 
 // Grid geometry handed to kernels.  The reference's grid is a cube of D^3 cells (knearests.cu:249); here the three
 // resolutions are independent (kn_problem has dimx / dimy / dimz, knearests.h:5-7): the default grid has cells that

@@ -68,6 +68,7 @@ namespace {
 
 constexpr int kTableRing = 5;                                             // table covers |dj|,|dk| <= 5
 constexpr int kTableSize = (2 * kTableRing + 1) * (2 * kTableRing + 1);  // 121 rows
+static_assert(kTableSize == KN_ROW_TABLE_SIZE, "kn_problem.num_cell_offsets reports the table size");
 constexpr float kMargin = 4e-3f;               // absolute slack on a cell-border distance, coordinate units
 constexpr float kShrink = 1.0f - 1.0f / 262144.0f;  // relative slack on a squared lower bound (1 - 2^-18)
 constexpr float kGrow = 1.0f + 1.0f / 262144.0f;

@@ -12,8 +12,12 @@
  * Differences a caller can observe (all within what the reference leaves undefined):
  *  - the layout is deterministic: cells in ascending cell id, points inside a cell in ascending
  *    original index; rows of kn_get_knearests are ascending in (squared distance, sorted index);
+ *  - the grid is not a cube unless asked for: dimx, dimy, dimz differ (narrow cells in x, cells as wide as the search
+ *    radius in y and z: knc_fast_dims in knearests_c.h).  The environment variable KN_GRID_DENSITY=3.1 gives the
+ *    reference's cube of 3.1 points per cell (knearests.cu:249).  The grid decides the cell order only;
  *  - d_ptrs has dimx*dimy*dimz + 1 entries (exclusive prefix sum; last = number of points);
- *  - there is no ring offset table: num_cell_offsets is 0, d_cell_offsets/d_cell_offset_dists NULL;
+ *  - there is no ring offset table of cells: num_cell_offsets is the size of the (dj, dk) row table the query
+ *    kernels use in its place (121), d_cell_offsets/d_cell_offset_dists are NULL;
  *  - d_cell_max holds ONE float: the largest search radius (squared) any query needed;
  *  - any number of points >= 1 is accepted (the reference exits below 11 545, knearests.cu:255-258),
  *    and the search is exact for any distribution (the reference silently stops after ring 15).
@@ -28,7 +32,7 @@
 typedef struct {
     int allocated_points;        /* number of input points                                  (knearests.h:4)  */
     int dimx, dimy, dimz;        /* grid resolution, cubic: round(cbrt(n / 3.1))            (knearests.h:5)  */
-    int num_cell_offsets;        /* always 0 here (no offset table)                         (knearests.h:6)  */
+    int num_cell_offsets;        /* rows of the (dj, dk) table: 121                         (knearests.h:6)  */
     int *d_cell_offsets;         /* always NULL here                                        (knearests.h:7)  */
     float *d_cell_offset_dists;  /* always NULL here                                        (knearests.h:8)  */
     float *d_cell_max;           /* 1 float: max squared search radius used                 (knearests.h:9)  */

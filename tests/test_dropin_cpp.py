@@ -71,8 +71,22 @@ def test_cli_driver_loads_xyz_like_the_reference_and_prints_its_lines(oracle, tm
     r = subprocess.run([str(cli), str(xyz), str(tmp_path / "nb.u32"), str(tmp_path / "pts.f32")],
                        capture_output=True, text=True)
     assert r.returncode == 0, r.stderr
-    for needle in ("bbox [", "kn_firstbuild: ", "kn_solve: ", "Grid:  points per cell:"):
-        assert needle in r.stderr
+    # the lines scripts around the reference's driver parse: bbox (test_knearests.cu:77), num_cell_offsets (ungated,
+    # knearests.cu:288), GPU memory used / kn_firstbuild / kn_solve (IF_VERBOSE, :342,200,376), Max visited ring
+    # (ungated, :389), the statistics of kn_print_stats (:461-464)
+    for needle in ("bbox [", "num_cell_offsets = 121", "GPU memory used: ", "kn_firstbuild: ", "kn_solve: ",
+                   "Max visited ring: ", "Grid:  points per cell:"):
+        assert needle in r.stderr, needle
+    import re
+    a, b = re.search(r"Max visited ring: ([0-9.eE+-]+) / ([0-9.eE+-]+)", r.stderr).groups()
+    assert float(b) == 5.0 and 1.0 < float(a) < 6.0
+    # second run: the cloud comes from the binary cache written beside the .xyz file, same bytes, same rows
+    assert (tmp_path / "cloud.xyz.f32").exists()
+    r2 = subprocess.run([str(cli), str(xyz), str(tmp_path / "nb2.u32"), str(tmp_path / "pts2.f32")],
+                        capture_output=True, text=True)
+    assert r2.returncode == 0 and "binary cache" in r2.stderr and "binary cache" not in r.stderr
+    assert (tmp_path / "pts2.f32").read_bytes() == (tmp_path / "pts.f32").read_bytes()
+    assert (tmp_path / "nb2.u32").read_bytes() == (tmp_path / "nb.u32").read_bytes()
     pts = np.fromfile(tmp_path / "pts.f32", np.float32).reshape(-1, 3)
     assert np.array_equal(pts, oracle.load_xyz(str(xyz)))  # loader == restated reference loader, bit for bit
     got = np.fromfile(tmp_path / "nb.u32", np.uint32).reshape(-1, 50)

@@ -7,9 +7,18 @@
 // scripts that parse the reference's output keep working.  Optionally writes the neighbour table in ORIGINAL
 // index space (the remap of :155-160) as raw u32.  The CPU kd-tree cross-check of the reference driver is not
 // part of the product (the kd-tree is the reference's; see oracle/ and tests/).
+//
+// Parsing a 100 M-point text file takes minutes, so the loaded and rescaled cloud is kept beside the source as
+// <points.xyz>.f32 (raw little-endian floats x y z, preceded by a 16-byte header: magic "KNF32\0\0\0" and the point
+// count as u64) and read from there the next time, as long as it is not older than the .xyz file.  KN_NO_CACHE=1
+// switches that off.
+#include <sys/stat.h>
+
 #include <algorithm>
+#include <cstdint>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <fstream>
 #include <iostream>
 #include <sstream>
@@ -60,11 +69,57 @@ static bool load_xyz(const char *path, std::vector<float> &xyz) {
     return true;
 }
 
+static const char kCacheMagic[8] = {'K', 'N', 'F', '3', '2', 0, 0, 0};
+
+static bool load_cache(const std::string &xyz_path, std::vector<float> &xyz) {
+    const std::string path = xyz_path + ".f32";
+    struct stat src, bin;
+    if (stat(xyz_path.c_str(), &src) != 0 || stat(path.c_str(), &bin) != 0 || bin.st_mtime < src.st_mtime) return false;
+    FILE *f = std::fopen(path.c_str(), "rb");
+    if (!f) return false;
+    char magic[8];
+    uint64_t n = 0;
+    bool ok = std::fread(magic, 1, 8, f) == 8 && std::memcmp(magic, kCacheMagic, 8) == 0 && std::fread(&n, 8, 1, f) == 1 &&
+              n > 0 && (uint64_t)bin.st_size == 16 + 12 * n;
+    if (ok) {
+        xyz.resize(3 * n);
+        ok = std::fread(xyz.data(), sizeof(float), 3 * n, f) == 3 * n;
+    }
+    std::fclose(f);
+    if (ok) {
+        float mn[3], mx[3];
+        bbox(xyz, mn, mx);  // same line as after a fresh load (test_knearests.cu:77)
+        std::cerr << "bbox [" << mn[0] << ":" << mx[0] << "], [" << mn[1] << ":" << mx[1] << ", [" << mn[2] << ":" << mx[2] << "]"
+                  << std::endl;
+        std::cerr << "(points from the binary cache " << path << ")" << std::endl;
+    } else {
+        xyz.clear();
+    }
+    return ok;
+}
+
+static void save_cache(const std::string &xyz_path, const std::vector<float> &xyz) {
+    const std::string path = xyz_path + ".f32", tmp = path + ".tmp";
+    FILE *f = std::fopen(tmp.c_str(), "wb");
+    if (!f) return;  // read-only directory: no cache, no error
+    const uint64_t n = xyz.size() / 3;
+    const bool ok = std::fwrite(kCacheMagic, 1, 8, f) == 8 && std::fwrite(&n, 8, 1, f) == 1 &&
+                    std::fwrite(xyz.data(), sizeof(float), xyz.size(), f) == xyz.size();
+    std::fclose(f);
+    if (ok) std::rename(tmp.c_str(), path.c_str());
+    else std::remove(tmp.c_str());
+}
+
 int main(int argc, char **argv) {
     if (argc < 2) { std::cerr << "Usage: " << argv[0] << " points.xyz [neighbors.u32] [normalized_points.f32]" << std::endl; return 1; }
     setenv("KN_VERBOSE", "1", 0);  // kn_firstbuild / kn_solve lines, as the reference prints with IF_VERBOSE
     std::vector<float> points;
-    if (!load_xyz(argv[1], points)) { std::cerr << argv[1] << ": could not load file" << std::endl; return 1; }
+    const char *nc = std::getenv("KN_NO_CACHE");
+    const bool use_cache = !(nc && std::atoi(nc) != 0);
+    if (!(use_cache && load_cache(argv[1], points))) {
+        if (!load_xyz(argv[1], points)) { std::cerr << argv[1] << ": could not load file" << std::endl; return 1; }
+        if (use_cache) save_cache(argv[1], points);
+    }
     const int nb_points = (int)(points.size() / 3);
     std::cerr << knc_version() << std::endl;
 
