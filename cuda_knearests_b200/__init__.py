@@ -25,12 +25,13 @@ MAX_K = 256
 
 # every symbol include/knearests_c.h declares (tests check that the library exports all of them)
 C_ABI_SYMBOLS = [
-    "knc_prepare", "knc_prepare_ex", "knc_solve", "knc_solve_to_host", "knc_free", "knc_trim", "knc_get_points", "knc_get_permutation",
+    "knc_prepare", "knc_prepare_ex", "knc_solve", "knc_solve_async", "knc_solve_finish", "knc_halo_flag_ptr",
+    "knc_solve_to_host", "knc_free", "knc_trim", "knc_get_points", "knc_get_permutation",
     "knc_get_knearests", "knc_get_knearests_original", "knc_get_stats", "knc_get_info", "knc_get_timings",
     "knc_grid_dim", "knc_fast_dims", "knc_last_error", "knc_version", "knc_generate_uniform_device", "knc_scan_cells_noalloc",
     "knc_slab_route", "knc_get_knearests_global", "knc_set_index_offset", "knc_get_permutation_global",
     "knc_get_dists", "knc_query_points", "knc_get_tags",
-    "knc_route_begin", "knc_route_scatter", "knc_route_end",
+    "knc_route_begin", "knc_route_scatter", "knc_route_end", "knc_route_begin_async", "knc_route_scatter_async",
     "knc_peer_alloc", "knc_peer_open", "knc_peer_close", "knc_peer_free",
 ]
 # the reference's own (C++-mangled) entry points, knearests.h:21-29
@@ -65,7 +66,8 @@ class Options(C.Structure):  # knc_options
                 ("points_on_device", C.c_int), ("grid_dim", C.c_int), ("z_begin", C.c_int),
                 ("z_end", C.c_int), ("own_z_begin", C.c_int), ("own_z_end", C.c_int),
                 ("search_scale", C.c_float), ("algorithm", C.c_int), ("point_stride", C.c_int),
-                ("grid_dims", C.c_int * 3)]
+                ("grid_dims", C.c_int * 3), ("stream", C.c_void_p), ("query_hint", C.c_int),
+                ("query_begin_hint", C.c_int), ("query_count_hint", C.c_int)]
 
 
 class Info(C.Structure):  # knc_info
@@ -107,8 +109,12 @@ def lib() -> C.CDLL:
         vp = C.c_void_p
         L.knc_prepare.argtypes = [vp, C.c_int, C.c_int, C.POINTER(vp)]
         L.knc_prepare_ex.argtypes = [vp, C.c_int, C.POINTER(Options), C.POINTER(vp)]
-        for nm in ("knc_solve", "knc_free"):
+        for nm in ("knc_solve", "knc_solve_async", "knc_solve_finish", "knc_free"):
             getattr(L, nm).argtypes = [vp]
+        L.knc_halo_flag_ptr.argtypes = [vp, C.POINTER(vp)]
+        L.knc_route_begin_async.argtypes = [vp, C.c_int, C.c_uint, C.c_int, C.c_int, C.POINTER(C.c_int), C.c_int, vp, vp,
+                                            C.POINTER(vp)]
+        L.knc_route_scatter_async.argtypes = [vp, C.POINTER(vp), C.POINTER(C.c_longlong), vp]
         for nm in ("knc_get_points", "knc_get_permutation", "knc_get_knearests", "knc_get_knearests_original"):
             getattr(L, nm).argtypes = [vp, vp]
         L.knc_solve_to_host.argtypes = [vp, vp, C.c_int]
@@ -171,7 +177,9 @@ class KnProblem:
     """
 
     def __init__(self, points, k: int = 0, density: float = 0.0, grid_dim: int = 0, slab=None,
-                 search_scale: float = 0.0, algorithm: int = 0, grid_dims=None):
+                 search_scale: float = 0.0, algorithm: int = 0, grid_dims=None, stream: int = 0, query_hint=None):
+        """stream: a cudaStream_t (integer) of the caller -- all work of the handle then runs there and the constructor
+        does not wait for the build (device input only); query_hint = (query_begin, query_count) of a slab handle."""
         self._h = C.c_void_p()
         opt = Options()
         opt.struct_size = C.sizeof(Options)
@@ -180,6 +188,9 @@ class KnProblem:
         opt.grid_dim = int(grid_dim)
         if grid_dims is not None:
             opt.grid_dims[0], opt.grid_dims[1], opt.grid_dims[2] = (int(v) for v in grid_dims)
+        opt.stream = int(stream) if stream else None
+        if query_hint is not None:
+            opt.query_hint, opt.query_begin_hint, opt.query_count_hint = 1, int(query_hint[0]), int(query_hint[1])
         opt.search_scale = float(search_scale)
         opt.algorithm = int(algorithm)
         if slab is not None:
@@ -188,7 +199,8 @@ class KnProblem:
             import torch
             if not points.is_cuda or points.dtype != torch.float32 or not points.is_contiguous():
                 raise ValueError("device input must be a contiguous CUDA float32 tensor [n,3] or [n,4]")
-            torch.cuda.current_stream(points.device).synchronize()  # the library works on its own stream
+            if not stream:
+                torch.cuda.current_stream(points.device).synchronize()  # the library works on its own stream
             stride = 4 if (points.dim() == 2 and points.shape[1] == 4) else 3
             opt.point_stride = stride
             n = points.numel() // stride
@@ -209,6 +221,21 @@ class KnProblem:
         _check(lib().knc_solve(self._h))
         self.info = self._info()
         return self
+
+    def solve_async(self) -> "KnProblem":  # first half of kn_solve: enqueue only
+        _check(lib().knc_solve_async(self._h))
+        return self
+
+    def solve_finish(self) -> "KnProblem":  # second half: wait, read the diagnostics, raise on a halo miss
+        _check(lib().knc_solve_finish(self._h))
+        self.info = self._info()
+        return self
+
+    def halo_flag_ptr(self) -> int:
+        """Device address of the count of this slab's queries that reached beyond their halo planes."""
+        ptr = C.c_void_p()
+        _check(lib().knc_halo_flag_ptr(self._h, C.byref(ptr)))
+        return int(ptr.value)
 
     def solve_to_host(self, out: np.ndarray | None = None, chunks: int = 8) -> np.ndarray:
         """kn_solve + kn_get_knearests overlapped (knc_solve_to_host); `out` should be page-locked."""

@@ -85,7 +85,7 @@ cudaError_t dev_alloc(void **p, size_t bytes, cudaStream_t st) { return kn_dev_a
 
 // Streams and events are recycled: creating and destroying them are kernel-mode driver calls that cost
 // a noticeable fraction of a millisecond each, more when several processes share the host (one per GPU).
-struct StreamKit { cudaStream_t stream; cudaEvent_t ev[4]; };
+struct StreamKit { cudaStream_t stream; cudaEvent_t ev[5]; };
 std::mutex g_kit_lock;
 std::vector<StreamKit> g_kits[64];
 
@@ -99,7 +99,7 @@ cudaError_t take_kit(int device, StreamKit *k) {
         }
     }
     cudaError_t e = cudaStreamCreateWithFlags(&k->stream, cudaStreamNonBlocking);
-    for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreate(&k->ev[i]);
+    for (int i = 0; i < 5 && e == cudaSuccess; ++i) e = cudaEventCreate(&k->ev[i]);
     return e;
 }
 
@@ -107,7 +107,7 @@ void give_kit(int device, const StreamKit &k) {
     std::lock_guard<std::mutex> hold(g_kit_lock);
     if (device >= 0 && device < 64 && g_kits[device].size() < 16) { g_kits[device].push_back(k); return; }
     cudaStreamDestroy(k.stream);
-    for (int i = 0; i < 4; ++i) cudaEventDestroy(k.ev[i]);
+    for (int i = 0; i < 5; ++i) cudaEventDestroy(k.ev[i]);
 }
 
 int default_k() {
@@ -118,15 +118,16 @@ int default_k() {
 
 void free_device_state(knc_problem *p) {
     cudaStream_t st = p->stream;
+    if (p->d_retry) { cudaFreeAsync(p->d_retry, st); p->d_retry = NULL; }
     void *ptrs[] = {p->pub.d_cell_max, p->pub.d_permutation, p->pub.d_counters, p->pub.d_ptrs,
                     p->pub.d_globcounter, p->pub.d_stored_points, p->pub.d_knearests, p->d_points4, p->d_diag, p->d_tags};
     for (void *q : ptrs)
         if (q) cudaFreeAsync(q, st);
-    if (st) {
-        cudaStreamSynchronize(st);
+    if (st) cudaStreamSynchronize(st);
+    if (p->kit_stream) {
         StreamKit k;
-        k.stream = st;
-        for (int i = 0; i < 4; ++i) k.ev[i] = p->ev[i];
+        k.stream = p->kit_stream;
+        for (int i = 0; i < 5; ++i) k.ev[i] = p->ev[i];
         give_kit(p->device, k);
     }
     if (p->copy_stream) cudaStreamDestroy(p->copy_stream);
@@ -181,6 +182,17 @@ int knc_grid_dim(int n, float density) {
     // knearests.cu:249 -- f32 divide, double pow, round
     int sz = (int)round(pow((double)((float)n / density), (double)1.0f / 3.0));
     return sz < 1 ? 1 : sz;
+}
+
+// Event times of the last prepare / solve, once their events have completed (bit 0: prepare, bit 1: solve).
+static void read_timings(knc_problem *p) {
+    if (p->timings_pending & 1) {
+        if (cudaEventSynchronize(p->ev[2]) == cudaSuccess) {
+            cudaEventElapsedTime(&p->t.h2d_ms, p->ev[0], p->ev[1]);
+            cudaEventElapsedTime(&p->t.build_ms, p->ev[1], p->ev[2]);
+        }
+        p->timings_pending &= ~1;
+    }
 }
 
 // Radius of the sphere expected to hold k + 2.5 sqrt(k) + 2 points at `rho` points per unit volume: the first search
@@ -257,9 +269,11 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     {
         StreamKit kit;
         CU(take_kit(p->device, &kit));
-        p->stream = kit.stream;
-        for (int i = 0; i < 4; ++i) p->ev[i] = kit.ev[i];
+        p->kit_stream = kit.stream;
+        for (int i = 0; i < 5; ++i) p->ev[i] = kit.ev[i];
     }
+    p->owns_stream = o.stream ? 0 : 1;
+    p->stream = o.stream ? (cudaStream_t)o.stream : p->kit_stream;
     st = p->stream;
     p->k = k; p->density = density; p->search_scale = o.search_scale > 0.f ? o.search_scale : 1.f;
     p->algorithm = o.algorithm;
@@ -307,20 +321,33 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     CU(cudaMemsetAsync(p->pub.d_cell_max, 0, sizeof(float), st));
     {   // the queries are the points of the owned planes: one contiguous run of sorted positions
         int range[2] = {0, n};
-        if (ozb != zb || oze != ze) {
+        const bool slab = ozb != zb || oze != ze;
+        if (slab && o.query_hint) {  // the caller knows (from the routing counts): no device->host read, no wait
+            range[0] = o.query_begin_hint;
+            range[1] = o.query_begin_hint + o.query_count_hint;
+            if (range[0] < 0 || o.query_count_hint < 0 || range[1] > n) {
+                rc = fail(KNC_ERR_INVALID, "knc_prepare: query hint [%d, +%d) does not fit %d points", o.query_begin_hint,
+                          o.query_count_hint, n);
+                goto out;
+            }
+        } else if (slab) {
+            if (!p->owns_stream) {
+                rc = fail(KNC_ERR_INVALID, "knc_prepare: a slab on the caller's stream needs query_hint (no host wait there)");
+                goto out;
+            }
             CU(cudaMemcpyAsync(&range[0], p->pub.d_ptrs + (size_t)(ozb - zb) * plane, sizeof(int),
                                cudaMemcpyDeviceToHost, st));
             CU(cudaMemcpyAsync(&range[1], p->pub.d_ptrs + (size_t)(oze - zb) * plane, sizeof(int),
                                cudaMemcpyDeviceToHost, st));
         }
-        CU(cudaStreamSynchronize(st));
+        if (p->owns_stream) CU(cudaStreamSynchronize(st));  // kn_prepare returns with the grid built (knearests.cu:196)
         p->query_begin = range[0];
         p->query_count = range[1] - range[0];
     }
     CU(dev_alloc((void **)&p->pub.d_knearests, sizeof(unsigned) * (size_t)(p->query_count > 0 ? p->query_count : 1) * k, st));
-    CU(cudaEventElapsedTime(&p->t.h2d_ms, p->ev[0], p->ev[1]));
-    CU(cudaEventElapsedTime(&p->t.build_ms, p->ev[1], p->ev[2]));
-    if (verbose()) {
+    p->timings_pending |= 1;  // ev[0..2] are read when somebody asks (knc_get_timings), not here: that would wait
+    if (p->owns_stream) read_timings(p);
+    if (verbose() && p->owns_stream) {
         fprintf(stderr, "kn_firstbuild: %g msec (n=%d, grid %dx%dx%d planes [%d,%d), k=%d, h2d %g msec)\n",
                 p->t.build_ms, n, dims[0], dims[1], dims[2], zb, ze, k, p->t.h2d_ms);
         // what the handle keeps on the device (knearests.cu:342 prints its own running total the same way)
@@ -359,34 +386,65 @@ static double first_radius(const knc_problem *p) {
     return radius_for(p->k, (double)p->pub.allocated_points / volume) * p->search_scale;
 }
 
+// Second half of a solve: wait for the stream, read the diagnostics, report.
+static int solve_finish_impl(knc_problem *p, const char *who) {
+    int rc = KNC_OK;
+    unsigned diag[KN_DIAG_WORDS] = {0};
+    cudaStream_t st = p->stream;
+    if (!(p->timings_pending & 2)) return fail(KNC_ERR_STATE, "%s: no solve in flight", who);
+    CU(cudaMemcpyAsync(diag, p->d_diag, sizeof(diag), cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));  // blocking, like knearests.cu:373
+    if (p->copy_stream) CU(cudaStreamSynchronize(p->copy_stream));
+    CU(cudaEventElapsedTime(&p->t.solve_ms, p->ev[3], p->ev[4]));
+    p->timings_pending &= ~2;
+    read_timings(p);
+    p->t.restarts = diag[0];  // restarts inside the general kernel + queries it took over from the fast one
+    p->t.handed_over_blocks = diag[4];  // last chunk's (the counter restarts with every chunk)
+    memcpy(&p->t.max_radius2, &diag[1], sizeof(float));
+    p->solved = 1;
+    if (verbose()) {
+        const GridGeom g = kn_make_geom(p->dims, p->z_begin, p->z_end);
+        fprintf(stderr, "kn_solve: %g msec\n", p->t.solve_ms);
+        fprintf(stderr, "Max search radius: %g cells (first guess %g cells, %u of %d queries restarted)\n",
+                sqrt((double)p->t.max_radius2) / g.wy, first_radius(p) / g.wy, diag[0], p->query_count);
+    }
+    if (diag[2])
+        rc = fail(KNC_ERR_HALO, "%s: %u queries reach beyond the halo planes [%d,%d) of this slab", who, diag[2],
+                  p->z_begin, p->z_end);
+out:
+    if (p->d_retry) { cudaFreeAsync(p->d_retry, st); p->d_retry = NULL; }
+    return rc;
+}
+
 // The query, optionally streamed to the host: the query range is cut into `chunks` pieces; the rows of
-// piece c travel device->host on a second stream while piece c+1 is being computed.
-static int solve_impl(knc_problem *p, unsigned int *out_knn_host, int chunks, const char *who) {
+// piece c travel device->host on a second stream while piece c+1 is being computed.  `finish`: wait and report
+// (knc_solve); otherwise only enqueue (knc_solve_async; knc_solve_finish does the rest).
+static int solve_impl(knc_problem *p, unsigned int *out_knn_host, int chunks, const char *who, bool finish) {
     int rc = KNC_OK;
     if (!p) return fail(KNC_ERR_INVALID, "%s: NULL handle", who);
+    if (p->timings_pending & 2) return fail(KNC_ERR_STATE, "%s: the previous knc_solve_async was not finished", who);
     cudaStream_t st = p->stream;
     const GridGeom g = kn_make_geom(p->dims, p->z_begin, p->z_end);
     // first-guess radius: sphere expected to hold k + 2.5 sqrt(k) + 2 points at the cloud's mean density
     const double r0 = first_radius(p);
-    unsigned diag[KN_DIAG_WORDS] = {0};
-    int *d_retry = NULL;  // scratch of the solve: queries the fast kernel hands to the general kernel
     const int force_general = p->algorithm;  // 0 auto, 1 general kernel only, 2 insertion kernel for every k
     if (chunks < 1 || !out_knn_host) chunks = 1;
     if (chunks > 64) chunks = 64;
     const int per = (p->query_count + chunks - 1) / chunks;
     cudaEvent_t done[64];
     int made = 0;
-    CU(dev_alloc((void **)&d_retry, sizeof(int) * kn_retry_ints(per), st));
+    // scratch of the solve: queries the fast kernels hand to the general kernel, blocks the tile kernel hands on
+    CU(dev_alloc((void **)&p->d_retry, sizeof(int) * kn_retry_ints(per), st));
     if (out_knn_host && !p->copy_stream) CU(cudaStreamCreateWithFlags(&p->copy_stream, cudaStreamNonBlocking));
     CU(cudaMemsetAsync(p->d_diag, 0, sizeof(unsigned) * KN_DIAG_WORDS, st));
-    CU(cudaEventRecord(p->ev[2], st));
+    CU(cudaEventRecord(p->ev[3], st));
     for (int c = 0; c < chunks; ++c) {
         const int q0 = c * per, qn = (p->query_count - q0) < per ? (p->query_count - q0) : per;
         if (qn <= 0) break;
         unsigned int *rows = p->pub.d_knearests + (size_t)q0 * p->k;
         if (c) CU(cudaMemsetAsync(p->d_diag + 3, 0, sizeof(unsigned) * 2, st));  // the retry and block lists start empty
         CU(kn_launch_query(p->d_points4, p->pub.d_ptrs, g, p->pub.allocated_points, p->k, p->query_begin + q0, qn,
-                           (float)(r0 * r0), rows, p->d_diag, d_retry, force_general, p->index_offset, NULL, st));
+                           (float)(r0 * r0), rows, p->d_diag, p->d_retry, force_general, p->index_offset, NULL, st));
         if (out_knn_host) {
             CU(cudaEventCreateWithFlags(&done[made], cudaEventDisableTiming));
             ++made;
@@ -396,35 +454,34 @@ static int solve_impl(knc_problem *p, unsigned int *out_knn_host, int chunks, co
                                cudaMemcpyDeviceToHost, p->copy_stream));
         }
     }
-    CU(cudaEventRecord(p->ev[3], st));
-    CU(cudaMemcpyAsync(diag, p->d_diag, sizeof(diag), cudaMemcpyDeviceToHost, st));
+    CU(cudaEventRecord(p->ev[4], st));
     CU(cudaMemcpyAsync(p->pub.d_cell_max, p->d_diag + 1, sizeof(float), cudaMemcpyDeviceToDevice, st));
-    CU(cudaStreamSynchronize(st));  // blocking, like knearests.cu:373
-    if (out_knn_host) CU(cudaStreamSynchronize(p->copy_stream));
-    CU(cudaEventElapsedTime(&p->t.solve_ms, p->ev[2], p->ev[3]));
-    p->t.restarts = diag[0];  // restarts inside the general kernel + queries it took over from the fast one
-    p->t.handed_over_blocks = diag[4];  // last chunk's (the counter restarts with every chunk)
-    memcpy(&p->t.max_radius2, &diag[1], sizeof(float));
-    p->solved = 1;
-    if (verbose()) {
-        fprintf(stderr, "kn_solve: %g msec\n", p->t.solve_ms);
-        fprintf(stderr, "Max search radius: %g cells (first guess %g cells, %u of %d queries restarted)\n",
-                sqrt((double)p->t.max_radius2) / g.wy, r0 / g.wy, diag[0], p->query_count);
-    }
-    if (diag[2])
-        rc = fail(KNC_ERR_HALO, "%s: %u queries reach beyond the halo planes [%d,%d) of this slab", who, diag[2],
-                  p->z_begin, p->z_end);
+    p->timings_pending |= 2;
 out:
-    for (int i = 0; i < made; ++i) cudaEventDestroy(done[i]);
-    if (d_retry) cudaFreeAsync(d_retry, st);
+    if (rc == KNC_OK && finish) rc = solve_finish_impl(p, who);
+    else if (rc != KNC_OK && p->d_retry) { cudaFreeAsync(p->d_retry, st); p->d_retry = NULL; }
+    for (int i = 0; i < made; ++i) cudaEventDestroy(done[i]);  // (the events' work is enqueued or done: safe to drop)
     return rc;
 }
 
-int knc_solve(knc_problem *p) { return solve_impl(p, NULL, 1, "knc_solve"); }
+int knc_solve_async(knc_problem *p) { return solve_impl(p, NULL, 1, "knc_solve_async", false); }
+
+int knc_solve_finish(knc_problem *p) {
+    if (!p) return fail(KNC_ERR_INVALID, "knc_solve_finish: NULL handle");
+    return solve_finish_impl(p, "knc_solve_finish");
+}
+
+int knc_halo_flag_ptr(knc_problem *p, const unsigned int **d_flag) {
+    if (!p || !d_flag) return fail(KNC_ERR_INVALID, "knc_halo_flag_ptr: NULL argument");
+    *d_flag = p->d_diag + 2;
+    return KNC_OK;
+}
+
+int knc_solve(knc_problem *p) { return solve_impl(p, NULL, 1, "knc_solve", true); }
 
 int knc_solve_to_host(knc_problem *p, unsigned int *out_knn, int chunks) {
     if (!out_knn) return fail(KNC_ERR_INVALID, "knc_solve_to_host: out_knn is NULL");
-    return solve_impl(p, out_knn, chunks > 0 ? chunks : 8, "knc_solve_to_host");
+    return solve_impl(p, out_knn, chunks > 0 ? chunks : 8, "knc_solve_to_host", true);
 }
 
 
@@ -594,6 +651,7 @@ int knc_get_info(knc_problem *p, knc_info *out) {
 
 int knc_get_timings(knc_problem *p, knc_timings *out) {
     if (!p || !out) return fail(KNC_ERR_INVALID, "knc_get_timings: NULL argument");
+    read_timings(p);  // a prepare on the caller's stream leaves its event times unread until somebody asks
     *out = p->t;
     return KNC_OK;
 }

@@ -22,12 +22,16 @@ struct knc_problem {
     long long cells;             // dimx * dimy * (z_end - z_begin)
     int query_begin, query_count;
     int solved;
+    int owns_stream;             // 0: the caller's stream (knc_options.stream): never synchronised by prepare, never recycled
+    int timings_pending;         // bit 0: prepare's events, bit 1: solve's events not yet read (read needs them complete)
+    int *d_retry;                // scratch of an asynchronous solve in flight (freed by knc_solve_finish)
     float4 *d_points4;           // [n] x, y, z, bits(own sorted position): what the query kernels read
     unsigned int *d_tags;        // [n] 4th word of every input record in sorted order (point_stride 4 only, else NULL)
     unsigned int *d_diag;        // [KN_DIAG_WORDS] restarts, max radius^2 bits, halo misses, retry count, block fallbacks
-    cudaStream_t stream;
+    cudaStream_t stream;         // where the handle's work runs: its own, or the caller's (knc_options.stream)
+    cudaStream_t kit_stream;     // the library-owned stream that came with the events (recycled at knc_free)
     cudaStream_t copy_stream;    // device->host row copies of knc_solve_to_host (created on first use)
-    cudaEvent_t ev[4];
+    cudaEvent_t ev[5];             // h2d start, build start, build end, solve start, solve end
     knc_timings t;
 };
 

@@ -919,11 +919,27 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
         if constexpr (NET == 32) { KN_SORT_NETWORK_32(KN_CE) } else { KN_SORT_NETWORK_64(KN_CE) }
 #undef KN_CE
     }
-    // exact: k strictly increasing truncated distances, and the k-th inside the TRUE sphere (the prefilter's is wider)
+    // Exact if the k-th lies inside the TRUE sphere (the prefilter's is wider) and the truncated distances decide the
+    // order.  Two EQUAL truncated distances next to each other inside the row (0.5 % of the queries have such a pair)
+    // only leave the order of those two open: it is settled below from their exact distances, once the row is staged.
+    // A tie at the k / k+1 border, or three in a row, still go to the retry kernel.
     const bool inside = (a[K_T - 1] | kSlotMask) <= __float_as_uint(r2);
-    bool exact = searched && inside;
+    // (Worth it for the 64-key variants only -- 7 bits truncated, more neighbours: k = 50 loses a third of its retries,
+    // 83.3 -> 77.6 ms at 100 M points; at k = 20 such pairs are 0.08 % of the queries and the bookkeeping cost more
+    // than the retries it saved.)
+    constexpr bool kSettleTies = NET == 64;
+    unsigned long long ties = 0;  // bit u: entries u and u + 1 have the same truncated distance
+    bool strictly = true;
 #pragma unroll
-    for (int u = 0; u < K_T; ++u) exact = exact && (a[u] >> kSlotBits) < (a[u + 1] >> kSlotBits);
+    for (int u = 0; u < K_T; ++u) {
+        if constexpr (kSettleTies) {
+            if ((a[u] >> kSlotBits) == (a[u + 1] >> kSlotBits)) ties |= 1ull << u;
+        } else {
+            strictly = strictly && (a[u] >> kSlotBits) < (a[u + 1] >> kSlotBits);
+        }
+    }
+    const bool exact = searched && inside && strictly && !(ties >> (K_T - 1)) && !(ties & (ties << 1));
+    if (!exact) ties = 0;
     if (valid && !exact)
         P.retry_list[atomicAdd(P.retry_count, 1u)] = q | ((cnt < K_T || (searched && !inside)) ? (int)0x80000000 : 0);
     report_diag(P, s, exact, exact ? __uint_as_float((a[K_T - 1] | kSlotMask)) : 0.f, 0u, tid);
@@ -946,6 +962,17 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
         uint2 *dst = reinterpret_cast<uint2 *>(OUT + lane * K_T);
 #pragma unroll
         for (int v = 0; v < K_T / 2; ++v) dst[v] = make_uint2(res[2 * v], res[2 * v + 1]);
+    }
+    if (ties) {  // rare, divergent: order each tied pair by its exact (d2, position) -- the records come from global memory
+        unsigned *row = OUT + lane * K_T;
+        do {
+            const int u = __ffsll((long long)ties) - 1;
+            ties &= ties - 1;
+            const unsigned pa = row[u], pb = row[u + 1];
+            const unsigned long long ka = make_key(__ldg(P.pts + (pa - P.index_offset)), s, (int)pa);
+            const unsigned long long kb = make_key(__ldg(P.pts + (pb - P.index_offset)), s, (int)pb);
+            if (kb < ka) { row[u] = pb; row[u + 1] = pa; }
+        } while (ties);
     }
     const int wrows = min(32, rows - 32 * warp);  // rows of this warp (<= 0: none)
     unsigned int *out = P.knn + (row0 + 32 * warp) * K_T;

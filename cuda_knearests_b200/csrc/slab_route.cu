@@ -25,8 +25,10 @@ constexpr int kMaxRanks = 32;
 
 struct RoutePlan {
     int nranks;
-    int lo[kMaxRanks];  // first plane rank d wants
-    int hi[kMaxRanks];  // one past the last plane rank d wants
+    int lo[kMaxRanks];   // first plane rank d wants
+    int hi[kMaxRanks];   // one past the last plane rank d wants
+    int own[kMaxRanks];  // first plane rank d OWNS (its queries live in [own[d], own[d + 1]))
+    int own_end;         // one past the last owned plane of the last rank
 };
 
 __device__ __forceinline__ int plane_of(float z, float Df, int D) {
@@ -51,12 +53,15 @@ constexpr int kRouteTile = kRouteThreads * kRouteItems;
 constexpr int kRouteRuns = kRouteItems * (kRouteThreads / 32);
 
 // per tile and destination: how many of the tile's points go there.  counts[d * nblocks + tile]
+// own_low (optional, [2][nranks] long long, zeroed by the caller): totals of the records that lie in the destination's
+// OWN planes / in its halo planes BELOW them (what the driver needs to know every rank's query range without a read-back)
 __global__ void __launch_bounds__(kRouteThreads)
 kn_route_count_kernel(const float *__restrict__ xyz, int n, float Df, int D, const __grid_constant__ RoutePlan pl,
-                      int nblocks, int *__restrict__ counts) {
+                      int nblocks, int *__restrict__ counts, unsigned long long *__restrict__ own_low) {
     __shared__ int s_cnt[kMaxRanks];
+    __shared__ int s_own[kMaxRanks], s_low[kMaxRanks];
     const int tid = threadIdx.x;
-    if (tid < kMaxRanks) s_cnt[tid] = 0;
+    if (tid < kMaxRanks) { s_cnt[tid] = 0; s_own[tid] = 0; s_low[tid] = 0; }
     const long long base = (long long)blockIdx.x * kRouteTile + tid;
     float z[kRouteItems];
 #pragma unroll
@@ -67,14 +72,32 @@ kn_route_count_kernel(const float *__restrict__ xyz, int n, float Df, int D, con
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < kRouteItems; ++r) {
-        const unsigned m = base + (long long)r * kRouteThreads < n ? dest_mask(plane_of(z[r], Df, D), pl) : 0u;
+        const bool in = base + (long long)r * kRouteThreads < n;
+        const int plane = plane_of(z[r], Df, D);
+        const unsigned m = in ? dest_mask(plane, pl) : 0u;
         for (int d = 0; d < pl.nranks; ++d) {
-            const unsigned b = __ballot_sync(0xffffffffu, (m >> d) & 1u);
+            const bool goes = (m >> d) & 1u;
+            const unsigned b = __ballot_sync(0xffffffffu, goes);
             if ((tid & 31) == 0 && b) atomicAdd(&s_cnt[d], __popc(b));
+            if (own_low) {  // uniform
+                const int o0 = pl.own[d], o1 = d + 1 < pl.nranks ? pl.own[d + 1] : pl.own_end;
+                const unsigned bo = __ballot_sync(0xffffffffu, goes && plane >= o0 && plane < o1);
+                const unsigned bl = __ballot_sync(0xffffffffu, goes && plane < o0);
+                if ((tid & 31) == 0) {
+                    if (bo) atomicAdd(&s_own[d], __popc(bo));
+                    if (bl) atomicAdd(&s_low[d], __popc(bl));
+                }
+            }
         }
     }
     __syncthreads();
-    if (tid < pl.nranks) counts[(size_t)tid * nblocks + blockIdx.x] = s_cnt[tid];
+    if (tid < pl.nranks) {
+        counts[(size_t)tid * nblocks + blockIdx.x] = s_cnt[tid];
+        if (own_low) {
+            if (s_own[tid]) atomicAdd(own_low + tid, (unsigned long long)s_own[tid]);
+            if (s_low[tid]) atomicAdd(own_low + pl.nranks + tid, (unsigned long long)s_low[tid]);
+        }
+    }
 }
 
 // one block per destination: exclusive scan of its row of per-block counts, total to totals[d]
@@ -220,76 +243,110 @@ struct knc_route {
     int *d_counts;       // [nranks][nblocks] per-block group sizes, then their exclusive scan
     long long *d_tot;    // [nranks] group totals
     long long counts[kMaxRanks];
+    int counts_known;    // knc_route_begin read the group sizes back; the asynchronous variant leaves them on the device
+    cudaStream_t stream; // where the last scatter ran (the scratch is freed in its order)
 };
 
-extern "C" int knc_route_begin(const float *d_xyz, int n, unsigned int first_id, int grid_dim, int nranks,
-                               const int *zsplit, int halo, knc_route **out, long long *out_counts) {
-    if (!d_xyz || !zsplit || !out || !out_counts || n < 0 || grid_dim < 1 || halo < 0)
-        return kn_set_error(KNC_ERR_INVALID, "knc_route_begin: bad argument");
+static int route_begin_impl(const float *d_xyz, int n, unsigned int first_id, int grid_dim, int nranks, const int *zsplit,
+                            int halo, cudaStream_t st, long long *d_counts3, knc_route **out, long long *out_counts,
+                            const char *who) {
+    if (!d_xyz || !zsplit || !out || n < 0 || grid_dim < 1 || halo < 0 || (!out_counts && !d_counts3))
+        return kn_set_error(KNC_ERR_INVALID, "%s: bad argument", who);
     if (nranks < 1 || nranks > kMaxRanks)
-        return kn_set_error(KNC_ERR_INVALID, "knc_route_begin: nranks = %d, supported 1..%d", nranks, kMaxRanks);
+        return kn_set_error(KNC_ERR_INVALID, "%s: nranks = %d, supported 1..%d", who, nranks, kMaxRanks);
     *out = nullptr;
     knc_route *r = (knc_route *)calloc(1, sizeof(knc_route));
-    if (!r) return kn_set_error(KNC_ERR_NOMEM, "knc_route_begin: out of host memory");
+    if (!r) return kn_set_error(KNC_ERR_NOMEM, "%s: out of host memory", who);
     r->d_xyz = d_xyz; r->n = n; r->grid_dim = grid_dim; r->first_id = first_id;
     r->pl.nranks = nranks;
+    r->pl.own_end = zsplit[nranks];
     for (int d = 0; d < nranks; ++d) {
         if (zsplit[d] > zsplit[d + 1] || zsplit[0] != 0 || zsplit[nranks] != grid_dim) {
             free(r);
-            return kn_set_error(KNC_ERR_INVALID, "knc_route_begin: zsplit must rise from 0 to grid_dim");
+            return kn_set_error(KNC_ERR_INVALID, "%s: zsplit must rise from 0 to grid_dim", who);
         }
         r->pl.lo[d] = zsplit[d] - halo;
         r->pl.hi[d] = zsplit[d + 1] + halo;
+        r->pl.own[d] = zsplit[d];
         if (zsplit[d] == zsplit[d + 1]) r->pl.lo[d] = r->pl.hi[d] = 0;  // an empty slab wants nothing
-        out_counts[d] = 0;
+        if (out_counts) out_counts[d] = 0;
     }
     r->nblocks = (n + kRouteTile - 1) / kRouteTile;
     cudaError_t e = cudaSuccess;
-    if (n > 0) {
-        cudaStream_t st = 0;
+    if (d_counts3) e = cudaMemsetAsync(d_counts3, 0, sizeof(long long) * 3 * nranks, st);
+    if (n > 0 && e == cudaSuccess) {
         e = kn_dev_alloc((void **)&r->d_counts, sizeof(int) * (size_t)nranks * r->nblocks, st);
-        if (e == cudaSuccess) e = kn_dev_alloc((void **)&r->d_tot, sizeof(long long) * kMaxRanks, st);
+        if (e == cudaSuccess && !d_counts3) e = kn_dev_alloc((void **)&r->d_tot, sizeof(long long) * kMaxRanks, st);
         if (e == cudaSuccess) {
-            kn_route_count_kernel<<<r->nblocks, kRouteThreads, 0, st>>>(d_xyz, n, (float)grid_dim, grid_dim, r->pl, r->nblocks,
-                                                                       r->d_counts);
-            kn_route_scan_kernel<<<nranks, 1024, 0, st>>>(r->d_counts, r->nblocks, r->d_tot);
-            e = cudaMemcpyAsync(r->counts, r->d_tot, sizeof(long long) * nranks, cudaMemcpyDeviceToHost, st);
+            long long *tot = d_counts3 ? d_counts3 : r->d_tot;  // [0, nranks): records per destination
+            kn_route_count_kernel<<<r->nblocks, kRouteThreads, 0, st>>>(
+                d_xyz, n, (float)grid_dim, grid_dim, r->pl, r->nblocks, r->d_counts,
+                d_counts3 ? reinterpret_cast<unsigned long long *>(d_counts3) + nranks : nullptr);
+            kn_route_scan_kernel<<<nranks, 1024, 0, st>>>(r->d_counts, r->nblocks, tot);
+            e = cudaGetLastError();
+            if (e == cudaSuccess && out_counts)
+                e = cudaMemcpyAsync(r->counts, tot, sizeof(long long) * nranks, cudaMemcpyDeviceToHost, st);
         }
-        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        if (e == cudaSuccess && out_counts) e = cudaStreamSynchronize(st);
     }
     if (e != cudaSuccess) {
-        if (r->d_counts) cudaFreeAsync(r->d_counts, 0);
-        if (r->d_tot) cudaFreeAsync(r->d_tot, 0);
+        if (r->d_counts) cudaFreeAsync(r->d_counts, st);
+        if (r->d_tot) cudaFreeAsync(r->d_tot, st);
         free(r);
-        return kn_set_error(KNC_ERR_CUDA, "knc_route_begin: %s", cudaGetErrorString(e));
+        return kn_set_error(KNC_ERR_CUDA, "%s: %s", who, cudaGetErrorString(e));
     }
-    for (int d = 0; d < nranks; ++d) out_counts[d] = r->counts[d];
+    if (out_counts) for (int d = 0; d < nranks; ++d) out_counts[d] = r->counts[d];
+    r->counts_known = out_counts != nullptr;
     *out = r;
     return KNC_OK;
 }
 
-extern "C" int knc_route_scatter(knc_route *r, void *const *dest_bufs, const long long *dest_first) {
-    if (!r || !dest_bufs || !dest_first) return kn_set_error(KNC_ERR_INVALID, "knc_route_scatter: NULL argument");
+extern "C" int knc_route_begin(const float *d_xyz, int n, unsigned int first_id, int grid_dim, int nranks,
+                               const int *zsplit, int halo, knc_route **out, long long *out_counts) {
+    if (!out_counts) return kn_set_error(KNC_ERR_INVALID, "knc_route_begin: bad argument");
+    return route_begin_impl(d_xyz, n, first_id, grid_dim, nranks, zsplit, halo, 0, nullptr, out, out_counts, "knc_route_begin");
+}
+
+extern "C" int knc_route_begin_async(const float *d_xyz, int n, unsigned int first_id, int grid_dim, int nranks,
+                                     const int *zsplit, int halo, void *stream, long long *d_counts3, knc_route **out) {
+    if (!d_counts3) return kn_set_error(KNC_ERR_INVALID, "knc_route_begin_async: bad argument");
+    return route_begin_impl(d_xyz, n, first_id, grid_dim, nranks, zsplit, halo, (cudaStream_t)stream, d_counts3, out, nullptr,
+                            "knc_route_begin_async");
+}
+
+static int route_scatter_impl(knc_route *r, void *const *dest_bufs, const long long *dest_first, cudaStream_t st, bool wait,
+                              const char *who) {
+    if (!r || !dest_bufs || !dest_first) return kn_set_error(KNC_ERR_INVALID, "%s: NULL argument", who);
     if (r->n == 0) return KNC_OK;
     RouteDest dst;
     for (int d = 0; d < r->pl.nranks; ++d) {
-        if (r->counts[d] > 0 && (!dest_bufs[d] || ((uintptr_t)dest_bufs[d] & 15u) || dest_first[d] < 0))
-            return kn_set_error(KNC_ERR_INVALID, "knc_route_scatter: destination %d has no usable buffer", d);
+        const bool used = r->counts_known ? r->counts[d] > 0 : true;  // without host counts every destination must be usable
+        if (used && (!dest_bufs[d] || ((uintptr_t)dest_bufs[d] & 15u) || dest_first[d] < 0))
+            return kn_set_error(KNC_ERR_INVALID, "%s: destination %d has no usable buffer", who, d);
         dst.buf[d] = reinterpret_cast<float4 *>(dest_bufs[d]);
         dst.first[d] = dest_first[d];
     }
-    kn_route_scatter_kernel<<<r->nblocks, kRouteThreads, 0, 0>>>(r->d_xyz, r->n, r->first_id, (float)r->grid_dim, r->grid_dim,
-                                                                r->pl, r->nblocks, r->d_counts, dst);
+    kn_route_scatter_kernel<<<r->nblocks, kRouteThreads, 0, st>>>(r->d_xyz, r->n, r->first_id, (float)r->grid_dim, r->grid_dim,
+                                                                 r->pl, r->nblocks, r->d_counts, dst);
     cudaError_t e = cudaGetLastError();
-    if (e == cudaSuccess) e = cudaStreamSynchronize(0);  // the records (also those sent to peers) have landed
-    if (e != cudaSuccess) return kn_set_error(KNC_ERR_CUDA, "knc_route_scatter: %s", cudaGetErrorString(e));
+    if (e == cudaSuccess && wait) e = cudaStreamSynchronize(st);  // the records (also those sent to peers) have landed
+    if (e != cudaSuccess) return kn_set_error(KNC_ERR_CUDA, "%s: %s", who, cudaGetErrorString(e));
+    r->stream = st;
     return KNC_OK;
+}
+
+extern "C" int knc_route_scatter(knc_route *r, void *const *dest_bufs, const long long *dest_first) {
+    return route_scatter_impl(r, dest_bufs, dest_first, 0, true, "knc_route_scatter");
+}
+
+extern "C" int knc_route_scatter_async(knc_route *r, void *const *dest_bufs, const long long *dest_first, void *stream) {
+    return route_scatter_impl(r, dest_bufs, dest_first, (cudaStream_t)stream, false, "knc_route_scatter_async");
 }
 
 extern "C" int knc_route_end(knc_route *r) {
     if (!r) return KNC_OK;
-    if (r->d_counts) cudaFreeAsync(r->d_counts, 0);
-    if (r->d_tot) cudaFreeAsync(r->d_tot, 0);
+    if (r->d_counts) cudaFreeAsync(r->d_counts, r->stream);  // stream-ordered: after the scatter that reads it
+    if (r->d_tot) cudaFreeAsync(r->d_tot, r->stream);
     free(r);
     return KNC_OK;
 }

@@ -67,6 +67,14 @@ typedef struct {
                                grid_dims, grid_dim, density, environment KN_GRID_DENSITY, else knc_fast_dims(n, k).
                                The grid decides the cell order (hence the permutation and the row numbering),
                                never which neighbours a point gets.                                       */
+    /* --- for callers that drive several GPUs and cannot afford a host synchronisation per call --- */
+    void *stream;           /* a cudaStream_t of the caller on the current device: the handle does ALL its work there
+                               (instead of on a stream of its own) and knc_prepare_ex returns without waiting for
+                               it -- which requires query_hint below in slab mode.  NULL: own stream, blocking. */
+    int query_hint;         /* 1: query_begin_hint / query_count_hint are the sorted positions of the owned planes'
+                               points (known to the caller from the routing counts): the prepare then needs no
+                               device->host read to learn them                                                    */
+    int query_begin_hint, query_count_hint;
 } knc_options;
 
 /* What the handle holds; device pointers are valid until knc_free. */
@@ -119,6 +127,15 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
 /* Replaces kn_solve (knearests.h:22, knearests.cu:348-392): the all-points kNN query.  Blocking.
  * May be called again; it recomputes the same rows. */
 int knc_solve(knc_problem *p);
+
+/* knc_solve in two halves: knc_solve_async enqueues the query on the handle's stream and returns;
+ * knc_solve_finish waits for it, reads the diagnostics and reports like knc_solve (KNC_ERR_HALO included).  Between
+ * the two the caller may enqueue more work on the same stream (the multi-GPU driver: the ranks' vote on
+ * knc_halo_flag_ptr).  knc_halo_flag_ptr: DEVICE address of the word that counts this slab's queries that reached
+ * beyond their halo planes (valid after knc_solve_async, in stream order; 0 = the halo was wide enough). */
+int knc_solve_async(knc_problem *p);
+int knc_solve_finish(knc_problem *p);
+int knc_halo_flag_ptr(knc_problem *p, const unsigned int **d_flag);
 
 /* knc_solve and kn_get_knearests in one call, overlapped: the query runs in `chunks` pieces (<= 0: 8) and
  * the rows of each finished piece are copied to out_knn (HOST, query_count*k unsigned; page-locked
@@ -228,6 +245,16 @@ int knc_route_begin(const float *d_xyz, int n, unsigned int first_id, int grid_d
                     int halo, knc_route **out, long long *out_counts);
 int knc_route_scatter(knc_route *r, void *const *dest_bufs, const long long *dest_first);
 int knc_route_end(knc_route *r);
+
+/* The same two steps WITHOUT host synchronisation, on a stream of the caller (a cudaStream_t, NULL = the default
+ * stream).  knc_route_begin_async leaves, in stream order, 3 * nranks counts in d_counts3 (DEVICE, long long): for every
+ * destination d the records it will receive from this rank, how many of them lie in d's OWN planes (they become d's
+ * queries), and how many lie in d's halo planes BELOW its own (they come before d's queries in sorted order) -- so that
+ * ONE all-gather of these rows tells every rank where its groups land, how many points and queries every rank holds
+ * and at which global sorted position each rank's queries begin.  knc_route_scatter_async enqueues the scatter. */
+int knc_route_begin_async(const float *d_xyz, int n, unsigned int first_id, int grid_dim, int nranks, const int *zsplit,
+                          int halo, void *stream, long long *d_counts3, knc_route **out);
+int knc_route_scatter_async(knc_route *r, void *const *dest_bufs, const long long *dest_first, void *stream);
 
 /* Receive buffers other processes of the node can write into (CUDA IPC): knc_peer_alloc = cudaMalloc + a 64-byte
  * handle to hand to the other ranks; knc_peer_open maps another rank's buffer into this process (peer access is

@@ -13,10 +13,19 @@ ap.add_argument("--k", type=int, default=20)
 ap.add_argument("--algorithm", type=int, default=0)
 ap.add_argument("--density", type=float, default=0.0)
 ap.add_argument("--steps", type=int, default=2)
+ap.add_argument("--search-scale", type=float, default=0.0)
+ap.add_argument("--yz-margin", type=float, default=0.0, help="y/z cell width over the first radius (library: 1.02)")
+ap.add_argument("--cells-per-point", type=float, default=1.0)
 a = ap.parse_args()
+dims = None
+if a.yz_margin > 0:
+    import math
+    r0 = (3 * (a.k + 2.5 * math.sqrt(a.k) + 2) / (4 * math.pi * a.n / 1e9)) ** (1 / 3)
+    dyz = int(1000 / (a.yz_margin * r0))
+    dims = (max(1, round(a.cells_per_point * a.n / dyz / dyz)), dyz, dyz)
 pts = K.generate_uniform_device(a.n)
 for _ in range(a.steps):
-    with K.KnProblem(pts, k=a.k, density=a.density, algorithm=a.algorithm) as p:
+    with K.KnProblem(pts, k=a.k, density=a.density, algorithm=a.algorithm, search_scale=a.search_scale, grid_dims=dims) as p:
         p.solve()
         t = p.timings()
 print({kk: (round(v, 3) if isinstance(v, float) else v) for kk, v in t.items()}, (p.info.dimx, p.info.dimy, p.info.dimz))

@@ -87,3 +87,78 @@ def test_emulated_ranks_reproduce_single_gpu_rows(kn, oracle, world, k, n):
     assert np.array_equal(np.concatenate(got_perm), want_perm)  # global permutation, slice by slice
     assert np.array_equal(np.concatenate(got_rows), want_rows)  # rows in global sorted positions
     assert np.array_equal(got_orig, want_orig)                  # rows in original ids
+
+
+@pytest.mark.parametrize("world,k,n", [(2, 20, 400_000), (5, 8, 700_000), (3, 50, 300_000)])
+def test_emulated_ranks_through_the_asynchronous_entry_points(kn, oracle, world, k, n):
+    """The calls the multi-GPU driver makes on its fast path, with the ranks emulated on one GPU: knc_route_begin_async
+    (counts stay on the device: records / own / low-halo per destination), knc_route_scatter_async into the destinations'
+    buffers, knc_prepare_ex on the caller's stream with the query range taken from the counts (no read-back), and
+    knc_solve_async / knc_solve_finish.  Rows and permutation slices, concatenated, are the single-GPU arrays."""
+    import torch
+    from cuda_knearests_b200 import slabs
+    L = kn.lib()
+    pts = oracle.generate_uniform(n, seed=20171004)
+    with kn.KnProblem(pts, k=k) as p:
+        p.solve()
+        want_rows, want_perm = p.get_knearests(), p.get_permutation()
+    dims, zsplit = slabs.grid_and_split(n, world, k)
+    D = dims[2]
+    halo = slabs.halo_planes(k, n, D)
+    dev = torch.from_numpy(pts).cuda()
+    side = torch.cuda.Stream()
+    st = C.c_void_p(side.cuda_stream)
+    zs = (C.c_int * (world + 1))(*zsplit)
+    torch.cuda.synchronize()
+    handles, counts = [], []
+    for r in range(world):                       # step 1 of every rank: count, counts left on the device
+        lo, hi = r * n // world, (r + 1) * n // world
+        c3 = torch.full((3 * world,), -1, dtype=torch.int64, device="cuda")
+        h = C.c_void_p()
+        chunk = dev[lo:hi].contiguous()
+        kn._check(L.knc_route_begin_async(C.c_void_p(chunk.data_ptr()), hi - lo, lo, D, world, zs, halo, st,
+                                          C.c_void_p(c3.data_ptr()), C.byref(h)))
+        handles.append((h, chunk))
+        counts.append(c3)
+    side.synchronize()
+    a = torch.stack(counts).cpu().numpy()        # what the all-gather delivers: a[s] = rank s's 3 rows
+    sent, own, low = a[:, :world], a[:, world:2 * world], a[:, 2 * world:]
+    plane = np.clip(np.floor(pts[:, 2] * np.float32(D) / np.float32(1000)).astype(np.int64), 0, D - 1)
+    for d in range(world):                       # the counts themselves, against numpy
+        zb, ze, ozb, oze = slabs.held_planes(zsplit, d, halo, D)
+        for s_ in range(world):
+            pl = plane[s_ * n // world:(s_ + 1) * n // world]
+            assert sent[s_, d] == ((pl >= zb) & (pl < ze)).sum()
+            assert own[s_, d] == ((pl >= ozb) & (pl < oze)).sum()
+            assert low[s_, d] == ((pl >= zb) & (pl < ozb)).sum()
+    incoming = sent.sum(axis=0)
+    recv = [torch.empty((int(incoming[d]) + 1, 4), dtype=torch.float32, device="cuda") for d in range(world)]
+    bufs = (C.c_void_p * world)(*[b.data_ptr() for b in recv])
+    for r in range(world):                       # step 2: every rank scatters straight into the destinations' buffers
+        first = (C.c_longlong * world)(*[int(sent[:r, d].sum()) for d in range(world)])
+        kn._check(L.knc_route_scatter_async(handles[r][0], bufs, first, st))
+        kn._check(L.knc_route_end(handles[r][0]))
+    got_rows, got_perm = [], []
+    base = 0
+    for d in range(world):                       # step 3: slab handles on the caller's stream, nothing read back
+        zb, ze, ozb, oze = slabs.held_planes(zsplit, d, halo, D)
+        qbegin, qcount = int(low[:, d].sum()), int(own[:, d].sum())
+        with kn.KnProblem(recv[d][:int(incoming[d])], k=k, grid_dims=dims, slab=(zb, ze, ozb, oze),
+                          stream=side.cuda_stream, query_hint=(qbegin, qcount)) as p:
+            assert (p.info.query_begin, p.info.query_count) == (qbegin, qcount)
+            kn._check(L.knc_set_index_offset(p._h, base - qbegin))
+            p.solve_async()
+            flag = torch.as_tensor(slabs._DevView(p.halo_flag_ptr(), (1,)), device="cuda")
+            p.solve_finish()
+            assert int(flag.item()) == 0
+            got_rows.append(p.get_knearests())
+            got_perm.append(torch.as_tensor(slabs._DevView(p.tags_ptr() + 4 * qbegin, (qcount,)), device="cuda").cpu().numpy().view(np.uint32))
+            assert p.timings()["build_ms"] > 0
+            base += qcount
+    assert base == n
+    assert np.array_equal(np.concatenate(got_perm), want_perm)
+    assert np.array_equal(np.concatenate(got_rows), want_rows)
+    # a slab on the caller's stream without the hint cannot learn its query range without waiting: refused
+    with pytest.raises(kn.KnError):
+        kn.KnProblem(recv[0][:int(incoming[0])], k=k, grid_dims=dims, slab=slabs.held_planes(zsplit, 0, halo, D),
+                     stream=side.cuda_stream)
