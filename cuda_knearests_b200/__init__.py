@@ -32,7 +32,7 @@ C_ABI_SYMBOLS = [
     "knc_slab_route", "knc_get_knearests_global", "knc_set_index_offset", "knc_get_permutation_global",
     "knc_get_dists", "knc_query_points", "knc_get_tags",
     "knc_route_begin", "knc_route_scatter", "knc_route_end", "knc_route_begin_async", "knc_route_scatter_async",
-    "knc_peer_alloc", "knc_peer_open", "knc_peer_close", "knc_peer_free",
+    "knc_peer_alloc", "knc_peer_open", "knc_peer_close", "knc_peer_free", "knc_prepare_multi", "knc_solve_multi",
 ]
 # the reference's own (C++-mangled) entry points, knearests.h:21-29
 CXX_ABI_SYMBOLS = [
@@ -141,6 +141,8 @@ def lib() -> C.CDLL:
         L.knc_set_index_offset.argtypes = [vp, C.c_longlong]
         L.knc_get_permutation_global.argtypes = [vp, vp, C.c_int, vp]
         L.knc_get_tags.argtypes = [vp, C.POINTER(vp)]
+        L.knc_prepare_multi.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
+        L.knc_solve_multi.argtypes = [vp, C.c_int, C.c_int, C.c_int, vp, vp]
         L.knc_last_error.restype = C.c_char_p
         L.knc_version.restype = C.c_char_p
         _lib = L
@@ -321,6 +323,18 @@ class KnProblem:
             self.free()
         except Exception:
             pass
+
+
+def prepare_multi(points, k: int = 0, ngpus: int = 0) -> KnProblem:
+    """kn_prepare over `ngpus` ranks of this process (knc_prepare_multi; <= 0: every device, more ranks than devices
+    share devices).  The handle answers solve / get_points / get_permutation / get_knearests / stats / free."""
+    arr = np.ascontiguousarray(points, np.float32).reshape(-1, 3)
+    self = KnProblem.__new__(KnProblem)
+    self._h = C.c_void_p()
+    self._keep = None
+    _check(lib().knc_prepare_multi(C.c_void_p(arr.ctypes.data), arr.shape[0], int(k), int(ngpus), C.byref(self._h)))
+    self.info = self._info()
+    return self
 
 
 # function-style mirror of knearests.h, for code that reads like the reference's test driver

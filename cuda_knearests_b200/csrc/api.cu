@@ -422,6 +422,12 @@ out:
 static int solve_impl(knc_problem *p, unsigned int *out_knn_host, int chunks, const char *who, bool finish) {
     int rc = KNC_OK;
     if (!p) return fail(KNC_ERR_INVALID, "%s: NULL handle", who);
+    if (p->multi) {  // a handle that spans several GPUs: every slab solves, blocking
+        if (!finish) return fail(KNC_ERR_STATE, "%s: not available on a multi-GPU handle", who);
+        rc = kn_multi_solve(p);
+        if (rc == KNC_OK && out_knn_host) rc = kn_multi_get(p, 2, out_knn_host);
+        return rc;
+    }
     if (p->timings_pending & 2) return fail(KNC_ERR_STATE, "%s: the previous knc_solve_async was not finished", who);
     cudaStream_t st = p->stream;
     const GridGeom g = kn_make_geom(p->dims, p->z_begin, p->z_end);
@@ -489,6 +495,7 @@ int knc_get_dists(knc_problem *p, float *out_d2) {
     int rc = KNC_OK;
     float *d_out = NULL;
     if (!p || !out_d2) return fail(KNC_ERR_INVALID, "knc_get_dists: NULL argument");
+    if (p->multi) return fail(KNC_ERR_STATE, "knc_get_dists: not available on a multi-GPU handle (its slabs live on several devices)");
     if (!p->solved) return fail(KNC_ERR_STATE, "knc_get_dists: call knc_solve first");
     {
         const size_t bytes = sizeof(float) * (size_t)p->query_count * p->k;
@@ -509,6 +516,7 @@ int knc_query_points(knc_problem *p, const float *xyz, int m, unsigned int *out_
     unsigned *d_rows = NULL, *d_diag = NULL;
     unsigned diag[4] = {0, 0, 0, 0};
     if (!p || !xyz || !out_knn || m < 1) return fail(KNC_ERR_INVALID, "knc_query_points: bad argument");
+    if (p->multi) return fail(KNC_ERR_STATE, "knc_query_points: not available on a multi-GPU handle (its slabs live on several devices)");
     {
         cudaStream_t st = p->stream;
         const GridGeom g = kn_make_geom(p->dims, p->z_begin, p->z_end);
@@ -543,6 +551,7 @@ out:
 
 int knc_set_index_offset(knc_problem *p, long long offset) {
     if (!p) return fail(KNC_ERR_INVALID, "knc_set_index_offset: NULL handle");
+    if (p->multi) return fail(KNC_ERR_STATE, "knc_set_index_offset: not available on a multi-GPU handle (its slabs live on several devices)");
     if (offset < 0 || offset + p->pub.allocated_points > 0xFFFFFFFEll)
         return fail(KNC_ERR_INVALID, "knc_set_index_offset: %lld + %d points does not fit 32-bit indices", offset,
                     p->pub.allocated_points);
@@ -552,6 +561,11 @@ int knc_set_index_offset(knc_problem *p, long long offset) {
 
 int knc_free(knc_problem *p) {
     if (!p) return KNC_OK;
+    if (p->multi) {
+        kn_multi_free(p);
+        free(p);
+        return KNC_OK;
+    }
     free_device_state(p);
     free(p);
     return KNC_OK;
@@ -567,17 +581,20 @@ out:
 }
 
 int knc_get_points(knc_problem *p, float *out_xyz) {
+    if (p && p->multi) return out_xyz ? kn_multi_get(p, 0, out_xyz) : fail(KNC_ERR_INVALID, "knc_get_points: NULL argument");
     return copy_out(p, out_xyz, p ? p->pub.d_stored_points : NULL, p ? sizeof(float) * 3 * (size_t)p->pub.allocated_points : 0,
                     "knc_get_points");
 }
 
 int knc_get_permutation(knc_problem *p, unsigned int *out_perm) {
+    if (p && p->multi) return out_perm ? kn_multi_get(p, 1, out_perm) : fail(KNC_ERR_INVALID, "knc_get_permutation: NULL argument");
     return copy_out(p, out_perm, p ? p->pub.d_permutation : NULL, p ? sizeof(unsigned) * (size_t)p->pub.allocated_points : 0,
                     "knc_get_permutation");
 }
 
 int knc_get_knearests(knc_problem *p, unsigned int *out_knn) {
     if (p && !p->solved) return fail(KNC_ERR_STATE, "knc_get_knearests: call knc_solve first");
+    if (p && p->multi) return out_knn ? kn_multi_get(p, 2, out_knn) : fail(KNC_ERR_INVALID, "knc_get_knearests: NULL argument");
     return copy_out(p, out_knn, p ? p->pub.d_knearests : NULL, p ? sizeof(unsigned) * (size_t)p->query_count * p->k : 0,
                     "knc_get_knearests");
 }
@@ -586,6 +603,7 @@ int knc_get_knearests_original(knc_problem *p, unsigned int *out_neighbors) {
     int rc = KNC_OK;
     unsigned *d_tmp = NULL;
     if (!p || !out_neighbors) return fail(KNC_ERR_INVALID, "knc_get_knearests_original: NULL argument");
+    if (p->multi) return fail(KNC_ERR_STATE, "knc_get_knearests_original: not available on a multi-GPU handle (its slabs live on several devices)");
     if (!p->solved) return fail(KNC_ERR_STATE, "knc_get_knearests_original: call knc_solve first");
     if (p->query_count != p->pub.allocated_points)
         return fail(KNC_ERR_INVALID, "knc_get_knearests_original: not available in slab mode");
@@ -604,6 +622,7 @@ out:
 
 int knc_get_tags(knc_problem *p, const unsigned int **d_tags) {
     if (!p || !d_tags) return fail(KNC_ERR_INVALID, "knc_get_tags: NULL argument");
+    if (p->multi) return fail(KNC_ERR_STATE, "knc_get_tags: not available on a multi-GPU handle (its slabs live on several devices)");
     if (!p->d_tags) return fail(KNC_ERR_STATE, "knc_get_tags: the handle was prepared with point_stride 3 (no 4th word)");
     *d_tags = p->d_tags;
     return KNC_OK;
@@ -616,8 +635,13 @@ int knc_get_stats(knc_problem *p, knc_stats *out) {
     memset(out, 0, sizeof(*out));
     h = (int *)malloc(sizeof(int) * (size_t)p->cells);
     if (!h) return fail(KNC_ERR_NOMEM, "knc_get_stats: out of host memory");
-    CU(cudaMemcpyAsync(h, p->pub.d_counters, sizeof(int) * (size_t)p->cells, cudaMemcpyDeviceToHost, p->stream));
-    CU(cudaStreamSynchronize(p->stream));
+    if (p->multi) {
+        rc = kn_multi_counters(p, h);
+        if (rc != KNC_OK) goto out;
+    } else {
+        CU(cudaMemcpyAsync(h, p->pub.d_counters, sizeof(int) * (size_t)p->cells, cudaMemcpyDeviceToHost, p->stream));
+        CU(cudaStreamSynchronize(p->stream));
+    }
     out->cells = p->cells;
     out->min_per_cell = INT_MAX;
     for (long long c = 0; c < p->cells; c++) {  // knearests.cu:455-460
@@ -651,7 +675,7 @@ int knc_get_info(knc_problem *p, knc_info *out) {
 
 int knc_get_timings(knc_problem *p, knc_timings *out) {
     if (!p || !out) return fail(KNC_ERR_INVALID, "knc_get_timings: NULL argument");
-    read_timings(p);  // a prepare on the caller's stream leaves its event times unread until somebody asks
+    if (!p->multi) read_timings(p);  // a prepare on the caller's stream leaves its event times unread until somebody asks
     *out = p->t;
     return KNC_OK;
 }
@@ -679,7 +703,9 @@ static void die_on(int rc, const char *where) {
 
 kn_problem *kn_prepare(float3 *points, int numpoints) {
     knc_problem *p = NULL;
-    die_on(knc_prepare((const float *)points, numpoints, 0, &p), "kn_prepare");
+    const char *g = getenv("KN_NUM_GPUS");  // several GPUs for callers of the reference's API: the same seven calls
+    if (g && atoi(g) > 1) die_on(knc_prepare_multi((const float *)points, numpoints, 0, atoi(g), &p), "kn_prepare");
+    else die_on(knc_prepare((const float *)points, numpoints, 0, &p), "kn_prepare");
     // printed unconditionally by the reference (knearests.cu:288); here: the rows of the (dj, dk) table that takes
     // the place of its list of cell offsets
     fprintf(stderr, "num_cell_offsets = %d\n", p->pub.num_cell_offsets);

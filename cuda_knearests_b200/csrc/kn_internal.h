@@ -6,10 +6,13 @@
 #include "knearests.h"
 #include "knearests_c.h"
 
+struct knc_multi;  // multi.cu: the slabs of a handle that spans several GPUs
+
 // The handle.  Its first member is the reference-compatible public struct (knearests.h), so a
 // kn_problem* handed to reference-style callers and a knc_problem* are the same address.
 struct knc_problem {
     kn_problem pub;
+    knc_multi *multi;            // non-NULL: a multi-GPU handle (knc_prepare_multi / KN_NUM_GPUS); the work is in its slabs
     int k;
     int device;
     float density;
@@ -92,6 +95,12 @@ cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const Gr
 cudaError_t kn_launch_rows_dists(const float4 *d_points4, const unsigned int *d_rows, const float *d_ext_queries,
                                  int query_begin, unsigned int index_offset, long long rows, int k, float *d_out,
                                  cudaStream_t st);
+
+// ---- multi.cu ----------------------------------------------------------------------------------
+int kn_multi_solve(knc_problem *parent);
+int kn_multi_get(knc_problem *parent, int what, void *dst);  // 0 sorted points, 1 permutation, 2 neighbour rows
+int kn_multi_counters(knc_problem *parent, int *host_counters);
+void kn_multi_free(knc_problem *parent);
 
 // ---- api.cu ------------------------------------------------------------------------------------
 int kn_set_error(int code, const char *fmt, ...);  // records the message knc_last_error() returns

@@ -264,6 +264,19 @@ int knc_peer_open(const unsigned char *handle64, void **d_ptr);
 int knc_peer_close(void *d_ptr);
 int knc_peer_free(void *d_ptr);
 
+/* ---- multi-GPU, ONE process (SURVEY 8e "API") -------------------------------------------------------
+ * No reference counterpart (single-GPU).  knc_prepare_multi is kn_prepare (knearests.cu:235-344) over
+ * `ngpus` ranks (<= 0: every device; more ranks than devices share devices): the host points are cut into ngpus
+ * chunks, routed into z-slabs + halo of the library's own grid (knc_fast_dims) with the scatter kernel storing
+ * straight into the other GPUs' memory (peer access), and every slab is built.  The handle then answers knc_solve,
+ * knc_get_points / knc_get_permutation / knc_get_knearests (the single-GPU arrays, gathered from the slabs),
+ * knc_get_stats, knc_get_info (no device pointers), knc_get_timings (slowest rank) and knc_free; a solve whose
+ * halo proves too thin rebuilds with a wider one.  The reference's seven entry points do the same when the
+ * environment variable KN_NUM_GPUS is set (> 1).  knc_solve_multi: prepare + solve + rows (+ permutation) in one
+ * call; out_rows: HOST n*k, out_perm: HOST n or NULL. */
+int knc_prepare_multi(const float *xyz, int n, int k, int ngpus, knc_problem **out);
+int knc_solve_multi(const float *xyz, int n, int k, int ngpus, unsigned int *out_rows, unsigned int *out_perm);
+
 /* Slab handles keep the single-GPU contract globally.  Because every rank holds its planes in global
  * order, local sorted position + a constant = GLOBAL sorted position (the constant: points in all lower
  * planes minus this handle's query_begin; the caller gets it from an all-gather of the ranks' query

@@ -162,3 +162,49 @@ def test_emulated_ranks_through_the_asynchronous_entry_points(kn, oracle, world,
     with pytest.raises(kn.KnError):
         kn.KnProblem(recv[0][:int(incoming[0])], k=k, grid_dims=dims, slab=slabs.held_planes(zsplit, 0, halo, D),
                      stream=side.cuda_stream)
+
+
+@pytest.mark.parametrize("ranks,k,n", [(2, 20, 300_000), (3, 50, 250_000), (5, 8, 600_000), (8, 20, 900_000)])
+def test_one_process_multi_gpu_handle_returns_the_single_gpu_arrays(kn, oracle, ranks, k, n):
+    """knc_prepare_multi (C ABI, one process, a host thread per rank; on a box with fewer GPUs than ranks the ranks
+    share devices -- same code path, the "peer" stores are local): kn_solve / kn_get_* on that handle give exactly
+    the arrays of the single-GPU handle, and the oracle's."""
+    pts = oracle.generate_uniform(n, seed=20171004)
+    g = oracle.Grid(pts, dims=oracle.fast_dims(n, k))
+    with kn.prepare_multi(pts, k=k, ngpus=ranks) as p:
+        assert (p.info.n, p.info.query_count, p.info.dimx, p.info.dimy, p.info.dimz) == (n, n, *g.dims)
+        p.solve()
+        rows, perm, spts, stats = p.get_knearests(), p.get_permutation(), p.get_points(), p.stats()
+        t = p.timings()
+        with pytest.raises(kn.KnError):
+            p.get_dists()                      # per-slab extras are refused on the spanning handle, loudly
+    assert np.array_equal(perm, g.permutation)
+    assert np.array_equal(spts, g.sorted_xyz)
+    assert np.array_equal(rows, g.knn_exact(k))
+    assert stats["total"] == n and stats["histogram"][:63] == np.bincount(g.counters, minlength=64)[:63].tolist()
+    assert t["solve_ms"] > 0 and t["build_ms"] > 0
+
+
+def test_solve_multi_in_one_call_and_the_dropin_caller_with_kn_num_gpus(kn, oracle, pts20k, tmp_path):
+    import os
+    import subprocess
+    from test_dropin_cpp import BIN, build_dropin
+    n, k = 120_000, 20
+    pts = oracle.generate_uniform(n, seed=5)
+    g = oracle.Grid(pts, dims=oracle.fast_dims(n, k))
+    rows = np.empty((n, k), np.uint32)
+    perm = np.empty(n, np.uint32)
+    kn._check(kn.lib().knc_solve_multi(C.c_void_p(pts.ctypes.data), n, k, 4, C.c_void_p(rows.ctypes.data), C.c_void_p(perm.ctypes.data)))
+    assert np.array_equal(perm, g.permutation) and np.array_equal(rows, g.knn_exact(k))
+    # the reference's seven entry points, unchanged caller (tests/cpp/dropin_main.cu), three ranks by environment
+    if not BIN.exists():
+        build_dropin()
+    pts20k.tofile(tmp_path / "points.f32")
+    r = subprocess.run([str(BIN), str(tmp_path / "points.f32"), str(tmp_path / "neighbors.u32")], capture_output=True,
+                       text=True, env={**os.environ, "KN_NUM_GPUS": "3"})
+    assert r.returncode == 0, r.stderr
+    got = np.fromfile(tmp_path / "neighbors.u32", np.uint32).reshape(-1, 50)
+    g = oracle.Grid(pts20k, dims=oracle.fast_dims(len(pts20k), 50))
+    want = np.empty_like(got)
+    want[g.permutation] = g.permutation[g.knn_exact(50)]
+    assert np.array_equal(got, want)
