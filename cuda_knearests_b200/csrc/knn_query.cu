@@ -763,19 +763,27 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
     }
 
     // ---- every lane: its windows of the 3 x 3 rows, in global sorted positions -----------------------------------
+    // row_lower_bound2 specialised for |dj|, |dk| <= 1 (same values): the gap to the row below is the query's offset
+    // in its cell, to the row above one cell less that, to its own row none -- a query outside the domain sits in a
+    // border cell and the row beyond that border does not exist.
     const float r2 = P.radius0_sq;
     int gb[9], ge[9];
+    {
+        const float lym = fmaxf(0.f, fmaf(s.fy, P.g.wy, -kMargin)), lyp = fmaxf(0.f, fmaf(1.f - s.fy, P.g.wy, -kMargin));
+        const float lzm = fmaxf(0.f, fmaf(s.fz, P.g.wz, -kMargin)), lzp = fmaxf(0.f, fmaf(1.f - s.fz, P.g.wz, -kMargin));
+        const float ly2[3] = {lym * lym, 0.f, lyp * lyp}, lz2[3] = {lzm * lzm, 0.f, lzp * lzp};
+        const bool ey[3] = {s.cj > 0, true, s.cj < Dy - 1}, ez[3] = {s.ck > zb, true, s.ck < ze - 1};
+        const int base0 = ((s.ck - zb) * Dy + s.cj) * Dx;
+        const float reach = kMargin * P.g.invwx + 1e-3f;
 #pragma unroll
-    for (int rr = 0; rr < 9; ++rr) {
-        const int dj = rr % 3 - 1, dk = rr / 3 - 1;
-        const int j = s.cj + dj, k = s.ck + dk;
-        gb[rr] = 0; ge[rr] = 0;
-        if (valid && j >= 0 && j < Dy && k >= zb && k < ze) {
-            const float lbyz2 = row_lower_bound2(s, dj, dk, P.g);
-            if (lbyz2 <= r2) {
-                int ilo, ihi;
-                row_x_range(s, r2, lbyz2, P.g.invwx, Dx, ilo, ihi);
-                const int base = ((k - zb) * Dy + j) * Dx;
+        for (int rr = 0; rr < 9; ++rr) {
+            const int dj = rr % 3 - 1, dk = rr / 3 - 1;
+            gb[rr] = 0; ge[rr] = 0;
+            const float lbyz2 = (ly2[dj + 1] + lz2[dk + 1]) * kShrink;
+            if (valid && ey[dj + 1] && ez[dk + 1] && lbyz2 <= r2) {
+                const float rxc = fmaf(sqrt_approx(r2 - lbyz2) * kGrow, P.g.invwx, reach);  // = row_x_range
+                const int ilo = max(0, min(Dx - 1, (int)floorf(s.tx - rxc))), ihi = max(0, min(Dx - 1, (int)floorf(s.tx + rxc)));
+                const int base = base0 + (dk * Dy + dj) * Dx;
                 gb[rr] = __ldg(P.ptrs + base + ilo);
                 ge[rr] = __ldg(P.ptrs + base + ihi + 1);
             }

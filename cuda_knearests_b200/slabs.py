@@ -35,7 +35,13 @@ def grid_and_split(n_total: int, world: int, k: int = 0, density: float = 0.0):
         D = K.grid_dim(n_total, density)
         dims = (D, D, D)
     else:
-        dims = K.fast_dims(n_total, k)
+        dx, dy, dz = K.fast_dims(n_total, k)
+        if dz >= 4 * world and dz % world:
+            # equal numbers of planes per rank: the slowest rank sets the pace, and 29 planes against 28 are 3.6 % more
+            # queries.  Fewer (thicker) planes keep the cells wider than the first search radius, as the tile kernel wants.
+            dz -= dz % world
+            dx = max(1, round(n_total / (dy * dz)))
+        dims = (dx, dy, dz)
     return dims, [(r * dims[2]) // world for r in range(world + 1)]
 
 
@@ -403,11 +409,13 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
         step()
     dist.barrier()
     torch.cuda.synchronize()
-    infos = []
+    infos, step_s = [], []
     with ClockSampler(local_rank) as clk:
         t0 = time.perf_counter()
         for _ in range(args.steps):
+            ts = time.perf_counter()
             infos.append(step())
+            step_s.append(time.perf_counter() - ts)   # every step ends with a host wait on this rank's stream
         torch.cuda.synchronize()
         dist.barrier()
         wall = time.perf_counter() - t0
@@ -511,6 +519,8 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
                 "verify": None if verify is None else {
                     "queries": sum(c["queries"] for c in checks), "mismatches": sum(c["mismatches"] for c in checks),
                     "per_rank": checks},
+                "step_ms_rank0": {"min": round(1e3 * min(step_s), 3), "median": round(1e3 * sorted(step_s)[len(step_s) // 2], 3),
+                                  "max": round(1e3 * max(step_s), 3)},
                 "queries_per_rank": queries, "halo_attempts": infos[-1]["attempts"],
                 "phase_ms_rank0_instrumented": {kk: round(v, 3) for kk, v in phase_ms.items()}}
         print(json.dumps(line), flush=True)

@@ -34,12 +34,16 @@ def main(rep, out):
         thr = sum(int(r[ix["Thread Instructions Executed"]]) for r in rows[2:])
         f.write(f"# warp instructions {tot}, thread instructions {thr}, active lanes/instruction {thr / max(tot, 1):.2f}\n")
         f.write("# line  warp-inst(M)  avg-active-lanes  stall-samples  SASS\n")
+        hot = max(int(r[ix["Instructions Executed"]]) for r in rows[2:])
+        wv = ix.get("L1 Wavefronts Shared")
+        f.write("# the hot loop = every instruction executed at least half as often as the most executed one\n")
         for n, r in enumerate(rows[2:]):
             ie = int(r[ix["Instructions Executed"]])
-            if ie * 200 < tot:
-                continue  # only instructions that are >= 0.5 % of the kernel
+            if 2 * ie < hot:
+                continue
+            smem = f" smem-wavefronts/inst {float(r[wv] or 0) / max(ie, 1):4.1f}" if wv is not None and float(r[wv] or 0) > 0 else ""
             f.write(f"{n:5d} {ie / 1e6:10.1f} {float(r[ix['Avg. Threads Executed']]):6.1f} {int(r[ix['# Samples']]):8d}  "
-                    f"{r[ix['Source']].strip()}\n")
+                    f"{r[ix['Source']].strip()}{smem}\n")
 
 
 if __name__ == "__main__":

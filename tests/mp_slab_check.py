@@ -23,7 +23,7 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     n, k = 700_000, 20
     pts = O.generate_uniform(n, seed=4242)
-    g = O.Grid(pts, dims=O.fast_dims(n, k))  # what slabs.solve_distributed uses when no density is named
+    g = O.Grid(pts, dims=slabs.grid_and_split(n, world, k)[0])  # the grid slabs.solve_distributed uses when no density is named
     want_rows, want_perm = g.knn_exact(k), g.permutation
     lo, hi = rank * n // world, (rank + 1) * n // world
     mine = torch.from_numpy(pts[lo:hi]).cuda()

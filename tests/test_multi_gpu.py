@@ -38,10 +38,10 @@ def test_emulated_ranks_reproduce_single_gpu_rows(kn, oracle, world, k, n):
     import torch
     from cuda_knearests_b200 import slabs
     pts = oracle.generate_uniform(n, seed=20171004)
-    with kn.KnProblem(pts, k=k, algorithm=3 if n > 20_000_000 else 0) as p:  # big case: reference rows without the pre-pass
+    dims, zsplit = slabs.grid_and_split(n, world, k)  # the library's own grid with planes in multiples of `world`, as the driver uses it
+    with kn.KnProblem(pts, k=k, grid_dims=dims, algorithm=3 if n > 20_000_000 else 0) as p:  # big case: reference rows without the pre-pass
         p.solve()
         want_rows, want_perm, want_orig = p.get_knearests(), p.get_permutation(), p.get_knearests_original()
-    dims, zsplit = slabs.grid_and_split(n, world, k)  # the library's own grid, as the multi-GPU driver uses it
     D = dims[2]
     halo = slabs.halo_planes(k, n, D)
     dev = torch.from_numpy(pts).cuda()
@@ -99,10 +99,10 @@ def test_emulated_ranks_through_the_asynchronous_entry_points(kn, oracle, world,
     from cuda_knearests_b200 import slabs
     L = kn.lib()
     pts = oracle.generate_uniform(n, seed=20171004)
-    with kn.KnProblem(pts, k=k) as p:
+    dims, zsplit = slabs.grid_and_split(n, world, k)
+    with kn.KnProblem(pts, k=k, grid_dims=dims) as p:
         p.solve()
         want_rows, want_perm = p.get_knearests(), p.get_permutation()
-    dims, zsplit = slabs.grid_and_split(n, world, k)
     D = dims[2]
     halo = slabs.halo_planes(k, n, D)
     dev = torch.from_numpy(pts).cuda()

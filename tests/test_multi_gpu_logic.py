@@ -92,4 +92,5 @@ def test_plan_matches_survey():
     # the library's own grid: planes as thick as the first search radius, so 2 planes of halo for every k
     for k in (8, 20, 32, 50):
         dims, zs = slabs.grid_and_split(100_000_000, 8, k)
-        assert dims[1] == dims[2] and zs[-1] == dims[2] and slabs.halo_planes(k, 100_000_000, dims[2]) == 2
+        assert dims[2] % 8 == 0 and 0 <= dims[1] - dims[2] < 8 and zs[-1] == dims[2]  # equal planes per rank
+        assert len(set(np.diff(zs))) == 1 and slabs.halo_planes(k, 100_000_000, dims[2]) == 2
