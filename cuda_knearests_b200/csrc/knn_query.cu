@@ -688,10 +688,18 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
     constexpr unsigned kSlotMask = CAP <= 64 ? 63u : 127u;  // low key bits that hold the buffer slot
     constexpr int kSlotBits = CAP <= 64 ? 6 : 7;
     static_assert(CAP <= 128, "slot must fit the low key bits");
-    // Shared memory: the tile, then one PRIVATE region per warp: candidate buffer [CAP][32] of 16-bit tile slots,
-    // span list [10][32].  Private, so that a warp that is done can stage its rows there without a block barrier.
-    constexpr int kBufBytes = CAP * 64, kSpanBytes = 10 * 128, kWarpBytes = kBufBytes + kSpanBytes;
-    static_assert(kWarpBytes >= 32 * K_T * 4, "a warp's rows are staged in its own buffer + span area");
+    // Shared memory: the tile, then one PRIVATE region per warp (private, so that a warp that is done can stage its
+    // rows there without a block barrier): CAP + 2 rows of 32 16-bit words, one column per lane.  A lane's column holds
+    // its candidate buffer growing UP from row 0 and its span list -- two rows per span, begin and end slot -- in the
+    // rows just below CAP, first span lowest; rows CAP and CAP + 1 hold the terminator.  Spans are consumed as the
+    // buffer grows, so the two share the column: the buffer may use every row below the next unread span (a lane that
+    // would need more is an overflow and goes to the retry kernel).  That sharing is what lets 5 blocks fit an SM.
+    // (Sharing is used where it buys a fifth block, the 32-key variants; the 64-key variants -- 3 blocks per SM either
+    // way, and 8 % slower with it at k = 50 -- keep their 9 spans in rows of their own above the buffer.)
+    constexpr bool kShareColumn = NET == 32;
+    constexpr int kTermRow = kShareColumn ? CAP : CAP + 18;  // the terminator's rows: kTermRow, kTermRow + 1
+    constexpr int kWarpBytes = (kTermRow + 2) * 64;
+    static_assert(kWarpBytes >= 32 * K_T * 4, "a warp's rows are staged in its own region");
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) unsigned long long s_bar;
     __shared__ int s_adj[32];      // per segment: tile slot = s_adj + global sorted position
@@ -700,8 +708,7 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     float4 *tile = reinterpret_cast<float4 *>(smem_raw);                                  // [TCAP] records
     unsigned char *mine = smem_raw + (size_t)TCAP * 16 + (size_t)warp * kWarpBytes;          // this warp's region
-    unsigned short *BUF = reinterpret_cast<unsigned short *>(mine) + lane;                   // [CAP][32] tile slots
-    unsigned *SP = reinterpret_cast<unsigned *>(mine + kBufBytes) + lane;                    // [10][32] spans
+    unsigned short *BUF = reinterpret_cast<unsigned short *>(mine) + lane;                   // [CAP + 2][32], this lane's column
     const int Dx = P.g.Dx, Dy = P.g.Dy, zb = P.g.zb, ze = P.g.ze;
     const long long row0 = (long long)blockIdx.x * QB;
     const int rows = (int)min((long long)QB, (long long)P.query_count - row0);
@@ -797,20 +804,36 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
     const int qi = qrow - s_ends[0];
     int nsp = 0;
 #pragma unroll
-    for (int rr = 0; rr < 9; ++rr)
-        if (ge[rr] > gb[rr]) {
-            const int adj = s_adj[qi * 9 + rr];
-            SP[nsp * 32] = (unsigned)(gb[rr] + adj) | ((unsigned)(ge[rr] + adj) << 16);
-            ++nsp;
+    for (int rr = 0; rr < 9; ++rr) nsp += ge[rr] > gb[rr] ? 1 : 0;
+    {
+        // Scan order: corner rows, face rows, the own row LAST -- the rows with the fewest points inside the sphere come
+        // first, while the buffer's limit (below the unread spans) is lowest.
+        constexpr int kOrder[9] = {0, 2, 6, 8, 1, 3, 5, 7, 4};
+        unsigned short *sp = BUF + (kTermRow - 2 * nsp) * 32;  // first span lowest, the last one just below the terminator
+#pragma unroll
+        for (int o = 0; o < 9; ++o) {
+            const int rr = kOrder[o];
+            if (ge[rr] > gb[rr]) {
+                const int adj = s_adj[qi * 9 + rr];
+                sp[0] = (unsigned short)(gb[rr] + adj);
+                sp[32] = (unsigned short)(ge[rr] + adj);
+                sp += 64;
+            }
         }
-    SP[nsp * 32] = 8u;  // terminator: begin 8 (parks inside the head of the tile), end 0 -- recognised by end == 0
+        BUF[kTermRow * 32] = 8;       // terminator: begin 8 (parks inside the head of the tile) ...
+        BUF[(kTermRow + 1) * 32] = 0; // ... end 0 -- recognised by end == 0
+    }
     const int my_slot = q + s_adj[qi * 9 + 4];
 
-    // Append pointer (shared-memory address of the lane's next free buffer entry), clamped once per chunk: a chunk
-    // may run kSelChunk entries past `wlim`, reaching wlim at all counts as an overflow.
+    // Append pointer (shared-memory address of the lane's next free buffer entry), clamped once per chunk to `wlim`,
+    // kSelChunk rows below the next unread span (a chunk may run kSelChunk entries past it): reaching the limit at any
+    // time counts as an overflow -- `slack` keeps the smallest distance seen when the limit moved.
     const unsigned wp0 = smem_addr(BUF);
-    const unsigned wlim = wp0 + (unsigned)(CAP - kSelChunk) * 64u;
+    const unsigned spterm = wp0 + (unsigned)kTermRow * 64u;  // the terminator entry
     unsigned wp = wp0;
+    unsigned wlim = wp0 + (unsigned)(CAP - kSelChunk) * 64u;  // (own span rows: the buffer's limit never moves)
+    if (kShareColumn) wlim = spterm - (unsigned)max(nsp - 1, 0) * 128u - 256u;  // below the SECOND span: the first is taken at once
+    int slack = 1 << 20;
 
     while (!mbar_try_wait(bar, 0)) {}  // the tile has landed
 
@@ -825,12 +848,10 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
         unsigned long long pxy;
         asm("mov.b64 %0, {%1, %2};" : "=l"(pxy) : "f"(s.px), "f"(s.py));
         int ph = lane;  // slot residue (mod 8) this lane must read at in the coming iteration: lane + 4 x (iteration & 1)
-        const unsigned t0 = SP[0];
-        int end = (int)(t0 >> 16);
-        int ts = (int)(t0 & 0xffffu);
+        unsigned spaddr = spterm - (unsigned)nsp * 128u;          // the entry the next switch reads: the first span ...
+        int ts = (int)BUF[(kTermRow - 2 * nsp) * 32], end = (int)BUF[(kTermRow - 2 * nsp + 1) * 32];  // ... which is taken here
+        spaddr = min(spaddr + 128u, spterm);
         ts -= (ts - ph) & 7;
-        const unsigned spterm = smem_addr(SP + nsp * 32);         // the terminator entry
-        unsigned spaddr = min(smem_addr(SP + 32), spterm);        // the entry the next switch reads
         auto fetch = [&](float4(&c)[kSelChunk], int at) {
 #pragma unroll
             for (int u = 0; u < kSelChunk; ++u) c[u] = tile[at + u];
@@ -850,23 +871,42 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
         };
         // One step along the lane's span list, straight-line predicated code (the compiler made a divergent branch
         // of it): the next chunk of the span, or -- past its end -- the first chunk of the next span, started on the
-        // slot residue of the coming iteration.
+        // slot residue of the coming iteration; the buffer's limit moves up with the span list.
         auto advance = [&]() {
-            asm volatile("{\n\t.reg .pred p;\n\t.reg .u32 t, b;\n\t"
-                         "add.s32 %0, %0, 4;\n\t"
-                         "xor.b32 %3, %3, 4;\n\t"
-                         "setp.ge.s32 p, %0, %1;\n\t"
-                         "@p ld.shared.u32 t, [%2];\n\t"
-                         "@p shr.u32 %1, t, 16;\n\t"
-                         "@p and.b32 b, t, 0xffff;\n\t"
-                         "@p sub.s32 t, b, %3;\n\t"
-                         "@p and.b32 t, t, 7;\n\t"
-                         "@p sub.s32 %0, b, t;\n\t"
-                         "@p add.u32 %2, %2, 128;\n\t"
-                         "@p min.u32 %2, %2, %4;\n\t}"
-                         : "+r"(ts), "+r"(end), "+r"(spaddr), "+r"(ph)
-                         : "r"(spterm)
-                         : "memory");
+            if constexpr (kShareColumn) {
+                asm volatile("{\n\t.reg .pred p;\n\t.reg .u32 t, b;\n\t"
+                             "add.s32 %0, %0, 4;\n\t"
+                             "xor.b32 %3, %3, 4;\n\t"
+                             "setp.ge.s32 p, %0, %1;\n\t"
+                             "@p ld.shared.u16 b, [%2];\n\t"
+                             "@p ld.shared.u16 %1, [%2+64];\n\t"
+                             "@p sub.s32 t, %4, %7;\n\t"         // distance to the limit that is about to move
+                             "@p min.s32 %5, %5, t;\n\t"
+                             "@p sub.s32 t, b, %3;\n\t"
+                             "@p and.b32 t, t, 7;\n\t"
+                             "@p sub.s32 %0, b, t;\n\t"
+                             "@p add.u32 %2, %2, 128;\n\t"
+                             "@p min.u32 %2, %2, %6;\n\t"
+                             "@p sub.u32 %4, %2, 256;\n\t}"       // kSelChunk rows below the next unread span
+                             : "+r"(ts), "+r"(end), "+r"(spaddr), "+r"(ph), "+r"(wlim), "+r"(slack)
+                             : "r"(spterm), "r"(wp)
+                             : "memory");
+            } else {
+                asm volatile("{\n\t.reg .pred p;\n\t.reg .u32 t, b;\n\t"
+                             "add.s32 %0, %0, 4;\n\t"
+                             "xor.b32 %3, %3, 4;\n\t"
+                             "setp.ge.s32 p, %0, %1;\n\t"
+                             "@p ld.shared.u16 b, [%2];\n\t"
+                             "@p ld.shared.u16 %1, [%2+64];\n\t"
+                             "@p sub.s32 t, b, %3;\n\t"
+                             "@p and.b32 t, t, 7;\n\t"
+                             "@p sub.s32 %0, b, t;\n\t"
+                             "@p add.u32 %2, %2, 128;\n\t"
+                             "@p min.u32 %2, %2, %4;\n\t}"
+                             : "+r"(ts), "+r"(end), "+r"(spaddr), "+r"(ph)
+                             : "r"(spterm)
+                             : "memory");
+            }
         };
         float4 ca[kSelChunk], cb[kSelChunk];
         fetch(ca, ts);
@@ -887,7 +927,7 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
     // ---- select (see kn_query_select_kernel): 32-bit keys = bits(d2) with the low bits replaced by the buffer slot ----
     asm volatile("" ::: "memory");  // the appends above were written behind the compiler's back
     const int cnt = (int)((wp - wp0) / 64u) - 1;  // candidates that passed the prefilter, the query itself not counted
-    const bool searched = valid && cnt >= K_T && wp < wlim;
+    const bool searched = valid && cnt >= K_T && wp < wlim && slack > 0;  // wlim ends kSelChunk rows below the terminator
     const int have = searched ? cnt + 1 : 0;
     unsigned a[NET];
     for (int base = 0, round = 0; round == 0 || __any_sync(0xffffffffu, have > base); ++round) {
@@ -902,7 +942,7 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const int slot = base + (g + j - lo);
-                    ti[j] = (g + j >= lo && slot < have) ? (int)BUF[slot * 32] : 0;
+                    ti[j] = (g + j >= lo && slot < have) ? (int)BUF[min(slot, kTermRow + 1) * 32] : 0;  // (the row index stays inside the warp's region even if the load is hoisted)
                 }
                 float4 rec[8];
 #pragma unroll
@@ -1141,8 +1181,8 @@ cudaError_t launch(const QueryParams &P, bool fast, bool tile_ok, cudaStream_t s
                 // Tile capacity in records: 9 rows x (the x-extent of QB queries + 2 x reach) at ~1 point per cell is
                 // ~1340 at k = 20, + head and padding (~110), + 4 sigma: the x-extent of 128 consecutive queries varies
                 // by sqrt(128) cells and all 9 rows follow it, sigma ~ 107 records (profiles/r2_notes.md).
-                constexpr int TCAP = K_T <= 20 ? 1920 : 2048;
-                const size_t tsmem = (size_t)TCAP * 16 + (size_t)(QB / 32) * ((size_t)CAP * 64 + 10 * 128);
+                constexpr int TCAP = K_T <= 20 ? 1824 : 2048;  // 1824: the most that lets 5 blocks share an SM at k <= 20
+                const size_t tsmem = (size_t)TCAP * 16 + (size_t)(QB / 32) * ((size_t)(CAP + (NET == 32 ? 2 : 20)) * 64);
                 e = cudaFuncSetAttribute(kn_query_tile_kernel<K_T, QB, NET, CAP, TCAP>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem);
                 if (e != cudaSuccess) return e;
