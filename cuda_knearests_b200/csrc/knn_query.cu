@@ -958,14 +958,41 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
             }
         }
         base += NET - lo;
+        // Round 0 sorts all NET keys.  Later rounds hold K_T + 1 sorted keys and NET - K_T - 1 new ones: the block of the
+        // last kTail keys (it contains every new one) is sorted DESCENDING, which leaves the whole array bitonic, and
+        // one bitonic merge -- log2(NET) stages -- sorts it: 140 compare-exchanges instead of 191 at k = 20, 252
+        // instead of 543 at k = 50.
+        // (Used where it pays: k = 50, 75.6 -> 70.2 ms at 100 M points.  At k = 20 and 32 the second network made the
+        // kernel larger and it ran 1 % slower -- instruction fetch already stalls this kernel -- so they sort again.)
+        constexpr int kTail = (NET == 64 && K_T + 1 >= NET - 16) ? 16 : NET;
+        if (round == 0 || kTail == NET) {
 #define KN_CE(i, j)                                     \
     {                                                   \
         const unsigned lo_ = min(a[i], a[j]);           \
         a[j] = max(a[i], a[j]);                         \
         a[i] = lo_;                                     \
     }
-        if constexpr (NET == 32) { KN_SORT_NETWORK_32(KN_CE) } else { KN_SORT_NETWORK_64(KN_CE) }
+            if constexpr (NET == 32) { KN_SORT_NETWORK_32(KN_CE) } else { KN_SORT_NETWORK_64(KN_CE) }
 #undef KN_CE
+        } else {
+#define KN_CE(i, j)                                                      \
+    {                                                                    \
+        const unsigned hi_ = max(a[NET - kTail + i], a[NET - kTail + j]); \
+        a[NET - kTail + j] = min(a[NET - kTail + i], a[NET - kTail + j]); \
+        a[NET - kTail + i] = hi_;                                        \
+    }
+            if constexpr (kTail == 16) { KN_SORT_NETWORK_16(KN_CE) } else if constexpr (kTail == 32) { KN_SORT_NETWORK_32(KN_CE) }
+#undef KN_CE
+#pragma unroll
+            for (int stride = NET / 2; stride >= 1; stride /= 2)
+#pragma unroll
+                for (int i = 0; i < NET; ++i)
+                    if ((i & stride) == 0) {
+                        const unsigned lo_ = min(a[i], a[i + stride]);
+                        a[i + stride] = max(a[i], a[i + stride]);
+                        a[i] = lo_;
+                    }
+        }
     }
     // Exact if the k-th lies inside the TRUE sphere (the prefilter's is wider) and the truncated distances decide the
     // order.  Two EQUAL truncated distances next to each other inside the row (0.5 % of the queries have such a pair)
