@@ -176,21 +176,31 @@ def main_reference(args, rank: int):
 def verify_against_oracle(torch, rows, idtable, ptrs, info, index_offset: int, n_total: int, k: int,
                           samples: int = 64, seed: int = 0):
     """After the timed region: sampled rows of what the engine just computed, checked by the CPU oracle
-    (brute force over the regenerated cloud -- the generator is counter-based, so any rank can rebuild all of it).
+    (brute force over the regenerated cloud -- the generator is counter-based, so any rank can rebuild any part).
       rows     device view [query_count, k]: neighbour rows (sorted positions + index_offset)
       idtable  device view [points held]: original id of every sorted position held (permutation / tags)
       ptrs     device view [cells held + 1]
-    Checks, per sampled query: (1) its row, mapped to original ids, is the brute-force k nearest (the test of
-    test_knearests.cu:194-232 with brute force in place of the kd-tree); (2) the query sits in the cell the
-    oracle's cellFromPoint gives its coordinates, that cell holds exactly the cloud's points of that cell, in
-    ascending original id (the permutation contract, knearests.cu:57)."""
+    The sampled queries sit in four cell planes of the handle (first, last, two in between; random rows inside), so
+    that only the slices of the cloud around those planes have to be kept: the cloud is regenerated chunk by chunk
+    and a point is kept if its z lies within R = 3 first-radii of a sampled query; a row is only accepted if its k-th
+    brute-force distance is below R (nothing outside the kept slices can then be closer).  Checks, per query:
+    (1) its row, mapped to original ids, is the brute-force k nearest (the test of test_knearests.cu:194-232 with
+    brute force in place of the kd-tree); (2) the query sits in the cell the oracle's cellFromPoint gives its
+    coordinates, and that cell holds exactly the cloud's points of that cell, in ascending original id (the
+    permutation contract, knearests.cu:57)."""
+    import math
     import numpy as np
     import oracle as O
     nq = int(info.query_count)
     if nq == 0:
         return {"queries": 0, "mismatches": 0}
     rng = np.random.default_rng(1234 + seed)
-    sel = np.unique(np.concatenate([[0, nq - 1, nq // 2], rng.integers(0, nq, max(0, samples - 3))])).astype(np.int64)
+    planes = max(1, int(info.z_end) - int(info.z_begin))
+    per_plane = max(1, nq // planes)
+    bases = sorted({0, nq // 3, (2 * nq) // 3, max(0, nq - per_plane)})
+    each = max(1, samples // len(bases))
+    sel = np.unique(np.concatenate([[0, nq - 1]] + [np.minimum(nq - 1, b + rng.integers(0, per_plane, each)) for b in bases]))
+    sel = sel.astype(np.int64)
     sel_t = torch.from_numpy(sel).to(rows.device)
     rows_sel = rows[sel_t].to(torch.int64) & 0xFFFFFFFF
     nb = rows_sel - int(index_offset)
@@ -198,13 +208,39 @@ def verify_against_oracle(torch, rows, idtable, ptrs, info, index_offset: int, n
     empty = (rows_sel == 0xFFFFFFFF).cpu().numpy()
     spos = sel + int(info.query_begin)                      # local sorted positions of the sampled queries
     qid = (idtable[torch.from_numpy(spos).to(rows.device)].to(torch.int64) & 0xFFFFFFFF).cpu().numpy()
-    cloud = O.generate_uniform(n_total, seed=SEED)
-    kk = min(k + 1, n_total)
-    want, want_d2 = O.brute_external(cloud, cloud[qid], kk, with_d2=True)
-    mism, reordered = 0, 0
+    qxyz = np.stack([O.generate_uniform(1, seed=SEED, first=int(i))[0] for i in qid])
+    r0 = (3.0 * (k + 2.5 * math.sqrt(k) + 2.0) / (4.0 * math.pi * (n_total / 1e9))) ** (1.0 / 3.0)
+    R = np.float32(3.0 * r0)
+    # the kept slices: z within R of a sampled query (merged intervals, looked up with searchsorted)
+    iv = sorted((float(z - R), float(z + R)) for z in qxyz[:, 2])
+    merged = [list(iv[0])]
+    for a_, b_ in iv[1:]:
+        if a_ <= merged[-1][1]:
+            merged[-1][1] = max(merged[-1][1], b_)
+        else:
+            merged.append([a_, b_])
+    los = np.array([m[0] for m in merged], np.float32)
+    his = np.array([m[1] for m in merged], np.float32)
+    keep_ids, keep_xyz = [], []
+    chunk = 20_000_000
+    for start in range(0, n_total, chunk):
+        pts = O.generate_uniform(min(chunk, n_total - start), seed=SEED, first=start)
+        z = pts[:, 2]
+        j = np.searchsorted(los, z, side="right") - 1
+        inside = (j >= 0) & (z <= his[np.maximum(j, 0)])
+        idx = np.nonzero(inside)[0]
+        keep_ids.append(idx.astype(np.int64) + start)
+        keep_xyz.append(pts[idx])
+    ids_sub = np.concatenate(keep_ids)
+    cloud = np.ascontiguousarray(np.concatenate(keep_xyz))
+    kk = min(k + 1, len(ids_sub))
+    want_loc, want_d2 = O.brute_external(cloud, qxyz, kk, with_d2=True)
+    mism, reordered, too_far = 0, 0, 0
     for r in range(len(sel)):
-        w = [int(v) for v in want[r] if int(v) != int(qid[r])][:k]   # the query itself is dropped (knearests.cu:123)
+        w = [int(ids_sub[v]) for v in want_loc[r] if int(ids_sub[v]) != int(qid[r])][:k]  # the query itself is dropped (knearests.cu:123)
         g = [int(v) for v, e in zip(got_ids[r], empty[r]) if not e]
+        if len(w) == k and not (want_d2[r][kk - 1] < R * R):
+            too_far += 1     # the slices could hide a closer point: this row proves nothing (not expected on uniform clouds)
         if g == w:
             continue
         if sorted(g) == sorted(w):
@@ -214,27 +250,24 @@ def verify_against_oracle(torch, rows, idtable, ptrs, info, index_offset: int, n
     # cell membership of the sampled queries
     dimx, dimy, dimz, zb = int(info.dimx), int(info.dimy), int(info.dimz), int(info.z_begin)
     L = O.lib()
-    cells = np.array([L.kno_cell_from_point(dimx, dimy, dimz, float(x), float(y), float(z)) for x, y, z in cloud[qid]],
-                     np.int64)
+    cells = np.array([L.kno_cell_from_point(dimx, dimy, dimz, float(x), float(y), float(z)) for x, y, z in qxyz], np.int64)
     local = cells - zb * dimx * dimy
     lo = ptrs[torch.from_numpy(local).to(rows.device)].cpu().numpy().astype(np.int64)
     hi = ptrs[torch.from_numpy(local + 1).to(rows.device)].cpu().numpy().astype(np.int64)
     cell_bad = int(((spos < lo) | (spos >= hi)).sum())
-    # every point of the cloud in those cells, by the oracle's cell function (vectorised, f32 like knearests.cu:23-28)
+    # every kept point's cell, by the oracle's cell function (vectorised, f32 like knearests.cu:23-28)
     def axis(v, d):
         return np.clip(np.floor((v * np.float32(d)) / np.float32(1000.0)), 0, d - 1).astype(np.int64)
-    flag = np.zeros(dimz, bool)
-    flag[cells // (dimx * dimy)] = True
-    cand = np.nonzero(flag[axis(cloud[:, 2], dimz)])[0]
-    sub = cloud[cand]
-    cid = axis(sub[:, 0], dimx) + dimx * (axis(sub[:, 1], dimy) + dimy * axis(sub[:, 2], dimz))
-    for c, a, b in zip(cells, lo, hi):
-        members = (idtable[int(a):int(b)].to(torch.int64) & 0xFFFFFFFF).cpu().numpy()
-        if not np.array_equal(members, cand[cid == c]):   # ascending original id = stable counting sort
+    cid = axis(cloud[:, 0], dimx) + dimx * (axis(cloud[:, 1], dimy) + dimy * axis(cloud[:, 2], dimz))
+    for c, a_, b_ in zip(cells, lo, hi):
+        members = (idtable[int(a_):int(b_)].to(torch.int64) & 0xFFFFFFFF).cpu().numpy()
+        if not np.array_equal(members, ids_sub[cid == c]):   # ascending original id = stable counting sort
             cell_bad += 1
-    return {"queries": int(len(sel)), "mismatches": int(mism + cell_bad), "rows_wrong": int(mism),
-            "cells_wrong": int(cell_bad), "tie_reordered": int(reordered),
-            "checker": "oracle brute force (kno_brute_external) over the regenerated cloud + cell membership"}
+    return {"queries": int(len(sel)), "mismatches": int(mism + cell_bad + too_far), "rows_wrong": int(mism),
+            "cells_wrong": int(cell_bad), "outside_kept_slices": int(too_far), "tie_reordered": int(reordered),
+            "points_kept": int(len(ids_sub)),
+            "checker": "oracle brute force (kno_brute_external) over the regenerated slices of the cloud around the "
+                       "sampled queries + cell membership"}
 
 
 def workload_config(args):
