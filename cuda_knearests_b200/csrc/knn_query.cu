@@ -1065,6 +1065,8 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
     }
 }
 
+constexpr int kRetryWarpFactor = 64;  // see kn_query_retry_warp_kernel
+
 // ===================================================================================== general path
 // Per-lane nested loops over rows and candidates, restarts with a growing radius, plain square rings
 // of rows beyond the table: exact for any input.  MODE 0: one thread per query of the range (used when
@@ -1081,6 +1083,7 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
     unsigned long long *L = smem + tid;
     const long long total = RETRY ? (long long)*P.retry_count : (long long)P.query_count;
     const long long stride = (long long)gridDim.x * QB;
+    if (RETRY && total <= (long long)gridDim.x * (QB / 32) * kRetryWarpFactor) return;  // a short list: the warp-per-query kernel took it
     if (RETRY && blockIdx.x == 0 && tid == 0 && total) atomicAdd(P.diag + 0, (unsigned)total);  // counted as restarts
 
     for (long long row0 = (long long)blockIdx.x * QB; row0 < total; row0 += stride) {
@@ -1187,6 +1190,183 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
     }
 }
 
+// ------------------------------------------------------------------------------ retry path, few queries
+// The same search as MODE 1 above for a SHORT retry list, one WARP per query.  The general kernel gives every query a
+// lane, and lanes of a warp that walk different rows and restart at different times run one after the other: fine
+// when a million retries keep the machine full (100 M points), ruinous for a small cloud, whose few thousand
+// retries -- a third of the reference's 20 k-point fixture lies at the domain's faces -- leave most of the GPU idle
+// while each warp serialises 32 searches (0.46 ms of the fixture's 0.49 ms).  Here the 32 lanes read 32 candidates of
+// a row at once and every candidate inside the sphere goes, by ballot, into the warp's buffer in shared memory; when
+// the sphere has been searched the warp sorts the buffer (bitonic, in place) and the first k keys are the row.  Too
+// few: a larger sphere; more than the buffer holds: a smaller one, and if that does not help (a heap of coincident
+// points) the warp falls back to keeping a sorted list of k by insertion, which is exact for anything.
+// The list counts as short when it holds at most kRetryWarpFactor queries per resident warp.
+__device__ __forceinline__ int retry_warp_cap(int k) {  // buffer entries per warp: a power of two, >= 8 k and >= 256
+    int c = 256;
+    while (c < 8 * k) c <<= 1;
+    return c;
+}
+
+template <int K_T, int QB>
+__global__ void __launch_bounds__(QB) kn_query_retry_warp_kernel(const __grid_constant__ QueryParams P) {
+    extern __shared__ unsigned long long smem[];  // [QB / 32][cap]: one buffer per warp
+    const int K = K_T ? K_T : P.k;
+    const int cap = retry_warp_cap(K);
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int Dx = P.g.Dx, Dy = P.g.Dy, zb = P.g.zb, ze = P.g.ze;
+    const float invw = P.g.invwx, wmin = fminf(P.g.wy, P.g.wz);
+    unsigned long long *B = smem + (size_t)(tid >> 5) * cap;
+    const long long total = (long long)*P.retry_count;
+    const long long warps = (long long)gridDim.x * (QB / 32);
+    if (total > warps * kRetryWarpFactor) return;  // a long list: the general kernel's turn
+    if (blockIdx.x == 0 && tid == 0 && total) atomicAdd(P.diag + 0, (unsigned)total);  // counted as restarts
+    for (long long slot = (long long)blockIdx.x * (QB / 32) + (tid >> 5); slot < total; slot += warps) {
+        const int entry = P.retry_list[slot];
+        const int q = entry & 0x7FFFFFFF;
+        const QueryGeom s = query_geom(__ldg(P.pts + q), P.g);
+        float r2 = entry < 0 ? P.radius0_sq * 2.25f : P.radius0_sq;
+        unsigned restarts = 0;
+        int cnt = 0;        // keys held (collect mode: inside the sphere; insertion mode: the sorted list)
+        bool pruned = false;
+        bool collect = true;
+        unsigned long long kth = ~0ull;
+        float bound2 = r2;
+
+        // insertion mode: sorted insertion into B[0..K) by the whole warp (every lane looks at the entries lane,
+        // lane + 32, ..; the number of entries below the new key is its place; the entries from there on move up by one)
+        auto insert = [&](unsigned long long cand) {
+            int pos = 0;
+            for (int i0 = 0; i0 < cnt; i0 += 32) {
+                const int i = i0 + lane;
+                const unsigned long long e = i < cnt ? B[i] : ~0ull;
+                pos += __popc(__ballot_sync(0xffffffffu, e < cand));
+            }
+            const int last = min(cnt, K - 1);  // highest index written
+            for (int i0 = ((last - pos) / 32) * 32; i0 >= 0; i0 -= 32) {  // from the top down, a chunk of 32 at a time
+                const int i = pos + i0 + lane;
+                const bool mv = i < last;
+                const unsigned long long e = mv ? B[i] : 0ull;
+                __syncwarp();
+                if (mv) B[i + 1] = e;
+                __syncwarp();
+            }
+            if (lane == 0) B[pos] = cand;
+            __syncwarp();
+            cnt = min(cnt + 1, K);
+        };
+
+        auto scan_row = [&](int dj, int dk) {  // warp-uniform
+            const int j = s.cj + dj, k = s.ck + dk;
+            if (j < 0 || j >= Dy || k < zb || k >= ze) return;
+            const float lbyz2 = row_lower_bound2(s, dj, dk, P.g);
+            if (lbyz2 > bound2) { pruned = true; return; }
+            int ilo, ihi;
+            row_x_range(s, bound2, lbyz2, invw, Dx, ilo, ihi);
+            if (ilo > 0 || ihi < Dx - 1) pruned = true;
+            if (ilo > ihi) return;
+            const int row = ((k - zb) * Dy + j) * Dx;
+            const int p0 = __ldg(P.ptrs + row + ilo), end = __ldg(P.ptrs + row + ihi + 1);
+            for (int base = p0; base < end; base += 32) {
+                const int p = base + lane;
+                unsigned long long key = ~0ull;
+                if (p < end && p != q) key = make_key(__ldg(P.pts + p), s, p);  // self excluded by position, knearests.cu:123
+                if (collect) {
+                    const bool in = (unsigned)(key >> 32) <= __float_as_uint(r2);  // d2 <= r2 (non-negative floats order like their bits)
+                    const unsigned m = __ballot_sync(0xffffffffu, in);
+                    const int at = cnt + __popc(m & ((1u << lane) - 1u));
+                    if (in && at < cap) B[at] = key;
+                    cnt += __popc(m);
+                } else {
+                    unsigned m = __ballot_sync(0xffffffffu, key < kth);
+                    while (m) {
+                        const int src = __ffs(m) - 1;
+                        m &= m - 1;
+                        const unsigned long long cand = __shfl_sync(0xffffffffu, key, src);
+                        if (cand < kth) {  // the k-th may have tightened since the ballot
+                            insert(cand);
+                            if (cnt == K) {
+                                kth = B[K - 1];
+                                bound2 = fminf(r2, __uint_as_float((unsigned)(kth >> 32)));
+                            }
+                        }
+                    }
+                }
+            }
+        };
+
+        int shrinks = 0;
+        while (true) {
+            cnt = 0; kth = ~0ull; bound2 = r2; pruned = false;
+            for (int e = 0; e < P.tab.n; ++e) {  // rows nearest-first
+                if (P.tab.lb2[e] > bound2) { pruned = true; break; }
+                scan_row(P.tab.dj[e], P.tab.dk[e]);
+            }
+            {   // beyond the table: plain square rings of rows (see the general kernel)
+                const int rmax = max(max(s.cj, Dy - 1 - s.cj), max(s.ck - zb, ze - 1 - s.ck));
+                for (int r = kTableRing + 1; r <= rmax; ++r) {
+                    const float lb = fmaxf(0.f, (float)(r - 1) * wmin - kMargin);
+                    if (lb * lb * kShrink > bound2) { pruned = true; break; }
+                    for (int dk = -r; dk <= r; ++dk)
+                        for (int dj = -r; dj <= r; dj += (abs(dk) == r ? 1 : 2 * r)) scan_row(dj, dk);
+                }
+            }
+            __syncwarp();
+            if (collect) {
+                if (cnt > cap) {                       // more than the buffer holds: a smaller sphere, or -- a heap of
+                    if (++shrinks > 3) collect = false;  // coincident points -- the insertion mode, exact for anything
+                    else r2 *= 0.5f;
+                    continue;
+                }
+                if (cnt >= K) break;                   // the sphere holds k points
+                if (!pruned && r2 == FLT_MAX) break;   // the whole grid was searched and every point taken: fewer than k exist
+                r2 = pruned ? r2 * 2.25f : FLT_MAX;    // every row was walked in full, but points beyond r2 were left out
+                ++restarts;
+            } else {
+                const float kd2 = __uint_as_float((unsigned)(kth >> 32));
+                if ((cnt == K && kd2 <= r2) || !pruned) break;
+                r2 = (cnt == K) ? kd2 : r2 * 2.25f;
+                ++restarts;
+            }
+        }
+        if (collect) {  // sort what the sphere held: bitonic network over the next power of two, ~0 padding sorts last
+            int n2 = 32;
+            while (n2 < cnt) n2 <<= 1;
+            for (int i = cnt + lane; i < n2; i += 32) B[i] = ~0ull;
+            __syncwarp();
+            for (int k2 = 2; k2 <= n2; k2 <<= 1)
+                for (int j = k2 >> 1; j > 0; j >>= 1) {
+                    for (int t = lane; t < n2 / 2; t += 32) {
+                        const int i = 2 * t - (t & (j - 1)), partner = i + j;
+                        const unsigned long long x = B[i], y = B[partner];
+                        if ((x > y) == ((i & k2) == 0)) { B[i] = y; B[partner] = x; }
+                    }
+                    __syncwarp();
+                }
+            cnt = min(cnt, K);
+            kth = cnt ? B[cnt - 1] : ~0ull;
+        }
+        report_diag(P, s, lane == 0, (cnt == K) ? __uint_as_float((unsigned)(kth >> 32)) : FLT_MAX, lane == 0 ? restarts : 0u, tid);
+        __syncwarp();
+        unsigned int *out = P.knn + (long long)(q - P.query_begin) * K;
+        for (int t = lane; t < K; t += 32) {
+            const unsigned v = t < cnt ? (unsigned)B[t] : KNC_EMPTY;
+            out[t] = v == KNC_EMPTY ? v : v + P.index_offset;
+        }
+        __syncwarp();
+    }
+}
+
+template <int K_T, int QB>
+cudaError_t launch_retry_warp(const QueryParams &P, unsigned blocks, cudaStream_t st) {
+    int cap = 256;
+    while (cap < 8 * P.k) cap <<= 1;  // = retry_warp_cap
+    const size_t bytes = sizeof(unsigned long long) * (size_t)cap * (QB / 32);
+    cudaError_t e = cudaFuncSetAttribute(kn_query_retry_warp_kernel<K_T, QB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e != cudaSuccess) return e;
+    kn_query_retry_warp_kernel<K_T, QB><<<blocks, QB, bytes, st>>>(P);
+    return cudaGetLastError();
+}
+
 template <int K_T, int QB>
 cudaError_t launch(const QueryParams &P, bool fast, bool tile_ok, cudaStream_t st) {
     const size_t list_bytes = sizeof(unsigned long long) * (size_t)P.k * QB;
@@ -1229,8 +1409,10 @@ cudaError_t launch(const QueryParams &P, bool fast, bool tile_ok, cudaStream_t s
         e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)list_bytes);
         if (e != cudaSuccess) return e;
-        const unsigned retry_blocks = blocks < 148u * 8u ? blocks : 148u * 8u;
+        const unsigned retry_blocks = 148u * 8u;  // fixed: both retry kernels loop over the list, and agree on "short" by this size
         kn_query_general_kernel<K_T, QB, 1><<<retry_blocks, QB, list_bytes, st>>>(P);
+        e = launch_retry_warp<K_T, QB>(P, retry_blocks, st);  // same grid: the two agree on "short"
+        if (e != cudaSuccess) return e;
     } else if (fast) {
         const size_t smem = list_bytes + sizeof(unsigned long long) * (size_t)(kSpanSlots + kQueueSlots) * QB;
         e = cudaFuncSetAttribute(kn_query_fast_kernel<K_T, QB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -1239,8 +1421,10 @@ cudaError_t launch(const QueryParams &P, bool fast, bool tile_ok, cudaStream_t s
         e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)list_bytes);
         if (e != cudaSuccess) return e;
-        const unsigned retry_blocks = blocks < 148u * 8u ? blocks : 148u * 8u;  // loops over the retry list
+        const unsigned retry_blocks = 148u * 8u;  // fixed: both retry kernels loop over the list
         kn_query_general_kernel<K_T, QB, 1><<<retry_blocks, QB, list_bytes, st>>>(P);
+        e = launch_retry_warp<K_T, QB>(P, retry_blocks, st);
+        if (e != cudaSuccess) return e;
     } else {
         e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)list_bytes);
