@@ -1,3 +1,3 @@
-python tools/_case.py
-python -m pytest tests/test_parity_gpu.py tests/test_random_differential_gpu.py tests/test_parity_reference_gpu.py tests/test_multi_gpu.py -x -q 2>&1 | tail -3
-python profiles/small_case.py pts20k 50; python profiles/small_case.py u300k 50; python profiles/small_case.py u900k 50
+run() { N=$1; shift; python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 295$((RANDOM%90+10)) bench.py --gpus $N "$@"; }
+run 4 --steps 20 --warmup 3 --no-e2e > gpurun_out/r2_bench_n4.json 2> gpurun_out/err4.log; tail -c 700 gpurun_out/r2_bench_n4.json; grep -v "^\*\|OMP_NUM" gpurun_out/err4.log | tail -3
+run 2 --steps 20 --warmup 3 --no-e2e > gpurun_out/r2_bench_n2.json 2> gpurun_out/err2.log; tail -c 700 gpurun_out/r2_bench_n2.json
