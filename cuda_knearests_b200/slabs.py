@@ -410,6 +410,9 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
     dist.barrier()
     torch.cuda.synchronize()
     infos, step_s = [], []
+    import gc
+    gc.collect()
+    gc.disable()  # a collection in the middle of a 5 ms step is 1-2 ms of host time on one rank, and everybody waits for it
     with ClockSampler(local_rank) as clk:
         t0 = time.perf_counter()
         for _ in range(args.steps):
@@ -419,6 +422,7 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
         torch.cuda.synchronize()
         dist.barrier()
         wall = time.perf_counter() - t0
+    gc.enable()
     t = torch.tensor([wall], dtype=torch.float64, device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
     wall = float(t.item())
