@@ -1385,15 +1385,17 @@ cudaError_t launch(const QueryParams &P, bool fast, bool tile_ok, cudaStream_t s
             constexpr int NET = K_T <= 20 ? 32 : 64, CAP = K_T <= 20 ? 56 : K_T <= 32 ? 92 : 100;  // 56 and 92: the most that still lets 6 resp. 4 blocks share an SM (228 KB)
             const size_t smem = (sizeof(unsigned) * CAP + sizeof(int2) * kSpanSlots) * QB;
             if (tile_ok) {
+                // the tile kernel's buffer for k <= 20: 60 rows (16-bit entries in a column shared with the span list)
+                constexpr int TCAPB = K_T <= 20 ? 60 : CAP;
                 // Tile capacity in records: 9 rows x (the x-extent of QB queries + 2 x reach) at ~1 point per cell is
                 // ~1340 at k = 20, + head and padding (~110), + 4 sigma: the x-extent of 128 consecutive queries varies
                 // by sqrt(128) cells and all 9 rows follow it, sigma ~ 107 records (profiles/r2_notes.md).
-                constexpr int TCAP = K_T <= 20 ? 1824 : 2048;  // 1824: the most that lets 5 blocks share an SM at k <= 20
-                const size_t tsmem = (size_t)TCAP * 16 + (size_t)(QB / 32) * ((size_t)(CAP + (NET == 32 ? 2 : 20)) * 64);
-                e = cudaFuncSetAttribute(kn_query_tile_kernel<K_T, QB, NET, CAP, TCAP>,
+                constexpr int TCAP = K_T <= 20 ? 1760 : 2048;  // 1760 (mean + 3.5 sigma) with 60 buffer rows: 5 blocks share an SM at k <= 20
+                const size_t tsmem = (size_t)TCAP * 16 + (size_t)(QB / 32) * ((size_t)(TCAPB + (NET == 32 ? 2 : 20)) * 64);
+                e = cudaFuncSetAttribute(kn_query_tile_kernel<K_T, QB, NET, TCAPB, TCAP>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem);
                 if (e != cudaSuccess) return e;
-                kn_query_tile_kernel<K_T, QB, NET, CAP, TCAP><<<blocks, QB, tsmem, st>>>(P);
+                kn_query_tile_kernel<K_T, QB, NET, TCAPB, TCAP><<<blocks, QB, tsmem, st>>>(P);
                 e = cudaFuncSetAttribute(kn_query_select_kernel<K_T, QB, NET, CAP, true>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
                 if (e != cudaSuccess) return e;
