@@ -295,11 +295,11 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
     if (stride == 4) CU(dev_alloc((void **)&p->d_tags, sizeof(unsigned) * (size_t)n, st));
     // temporaries of the build
     s.tile_count = kn_build_scratch_tiles(cells);
-    CU(dev_alloc((void **)&s.d_cellid, sizeof(int) * (size_t)n, st));
-    CU(dev_alloc((void **)&s.d_rank, sizeof(int) * (size_t)n, st));
+    CU(dev_alloc((void **)&s.d_recs, sizeof(float4) * (size_t)n, st));
+    if (stride == 4) CU(dev_alloc((void **)&s.d_rec_tags, sizeof(unsigned) * (size_t)n, st));
     CU(dev_alloc((void **)&s.d_tile, sizeof(unsigned long long) * s.tile_count, st));
     CU(dev_alloc((void **)&s.d_ticket, sizeof(int) * 2, st));
-    CU(dev_alloc((void **)&s.d_biglist, sizeof(int) * ((size_t)n / KN_BIG_CELL + 1), st));
+    CU(dev_alloc((void **)&s.d_biglist, sizeof(int) * ((size_t)n / (KN_BIG_CELL + 1) + 1), st));
     if (n >= KN_BIN_MIN_POINTS && o.algorithm != 3) {  // algorithm 3: build without the z-band pre-pass (A/B, tests)
         CU(dev_alloc((void **)&s.d_bin_recs, sizeof(float4) * (size_t)n, st));
         CU(dev_alloc((void **)&s.d_bin_counts, sizeof(int) * kn_bin_counts_ints(n), st));
@@ -360,7 +360,7 @@ int knc_prepare_ex(const float *xyz, int n, const knc_options *opt, knc_problem 
 out:
     if (!o.points_on_device && d_in) cudaFreeAsync(d_in, st);
     {
-        void *tmp[] = {s.d_cellid, s.d_rank, s.d_tile, s.d_ticket, s.d_biglist, s.d_bin_recs, s.d_bin_counts, s.d_bin_tags};
+        void *tmp[] = {s.d_recs, s.d_rec_tags, s.d_tile, s.d_ticket, s.d_biglist, s.d_bin_recs, s.d_bin_counts, s.d_bin_tags};
         for (void *q : tmp)
             if (q) cudaFreeAsync(q, st);
     }

@@ -64,14 +64,14 @@ inline GridGeom kn_make_geom(const int dims[3], int zb, int ze) {
 
 // ---- grid_build.cu -----------------------------------------------------------------------------
 struct BuildScratch {
-    int *d_cellid;               // [n]
-    int *d_rank;                 // [n]
+    float4 *d_recs;              // [n] records in cell order, arrival order inside a cell
+    unsigned int *d_rec_tags;    // [n] their 4th input words (point_stride 4, else NULL)
     unsigned long long *d_tile;  // scan tile states
     int *d_ticket;               // scan ticket + big-cell worklist counter
-    int *d_biglist;              // [n / KN_BIG_CELL + 1] cells too large for the per-thread ordering
+    int *d_biglist;              // [n / (KN_BIG_CELL + 1) + 1] cells too large for the per-thread ordering
     size_t tile_count;
     float4 *d_bin_recs;          // [n] z-banded copy of the input (large clouds only, else NULL)
-    int *d_bin_counts;           // [kn_bin_counts_ints(n)] per-block band counts + band totals
+    int *d_bin_counts;           // [kn_bin_counts_ints(n)] band totals + band cursors
     unsigned int *d_bin_tags;    // [n] 4th input words in banded order (large clouds with point_stride 4, else NULL)
 };
 size_t kn_bin_counts_ints(int n);
@@ -106,4 +106,4 @@ void kn_multi_free(knc_problem *parent);
 int kn_set_error(int code, const char *fmt, ...);  // records the message knc_last_error() returns
 cudaError_t kn_dev_alloc(void **p, size_t bytes, cudaStream_t st);  // stream-ordered, from the library's private pool
 
-#define KN_BIG_CELL 32  // cells with more points than this are ordered by a whole block, not a thread
+#define KN_BIG_CELL 32  // a cell whose records see more than this many of their own kind to one side is ordered by a whole block

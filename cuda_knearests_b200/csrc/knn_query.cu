@@ -56,6 +56,7 @@
 #include <float.h>
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "kn_internal.h"
 #include "sort_network.h"
@@ -97,6 +98,7 @@ struct QueryParams {
     unsigned int *block_count;
     int halo_cells;        // tile kernel: cells staged beyond the block's own x-range on either side
     int bulk_rows_ok;      // tile kernel: the row array is 16-byte aligned, rows may leave as one bulk copy
+    float retry_grow;      // retry kernels: factor on the squared radius when a sphere held fewer than k points
     RowTable tab;
 };
 
@@ -1097,7 +1099,7 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
 
         int cnt = 0;
         unsigned long long kth = ~0ull;
-        float r2 = (RETRY && entry < 0) ? P.radius0_sq * 2.25f : P.radius0_sq;
+        float r2 = (RETRY && entry < 0) ? P.radius0_sq * P.retry_grow : P.radius0_sq;
         float bound2 = r2;
         bool pruned = false;
         unsigned restarts = 0;
@@ -1161,7 +1163,7 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
             if ((cnt == K && kd2 <= r2) || !pruned) {
                 done = true;  // everything within the k-th distance was searched, or the whole grid was
             } else {
-                r2 = (cnt == K) ? kd2 : r2 * 2.25f;  // the k-th found is a proven sufficient radius
+                r2 = (cnt == K) ? kd2 : r2 * (RETRY ? P.retry_grow : 2.25f);  // the k-th found is a proven sufficient radius
                 ++restarts;
             }
         }
@@ -1496,6 +1498,11 @@ cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const Gr
     const bool tile_ok = force_general != 4 && radius0_sq < reach * reach * kShrink;
     P.halo_cells = (int)ceilf(r0 * kGrow * g.invwx + kMargin * g.invwx + 1e-3f) + 1;  // >= row_x_range's reach, in cells
     P.bulk_rows_ok = ((uintptr_t)d_knn & 15u) == 0;
+    {
+        static float grow_env = -1.f;
+        if (grow_env < 0.f) { const char *e = getenv("KN_RETRY_GROW"); grow_env = e ? (float)atof(e) : 0.f; }
+        P.retry_grow = grow_env > 1.f ? grow_env : 2.25f;
+    }
     switch (k) {
         case 8: return launch<8, 128>(P, fast, tile_ok, st);
         case 20: return launch<20, 128>(P, fast, tile_ok, st);

@@ -16,6 +16,7 @@ ap.add_argument("--steps", type=int, default=2)
 ap.add_argument("--search-scale", type=float, default=0.0)
 ap.add_argument("--yz-margin", type=float, default=0.0, help="y/z cell width over the first radius (library: 1.02)")
 ap.add_argument("--cells-per-point", type=float, default=1.0)
+ap.add_argument("--no-solve", action="store_true", help="grid build only")
 a = ap.parse_args()
 dims = None
 if a.yz_margin > 0:
@@ -26,6 +27,7 @@ if a.yz_margin > 0:
 pts = K.generate_uniform_device(a.n)
 for _ in range(a.steps):
     with K.KnProblem(pts, k=a.k, density=a.density, algorithm=a.algorithm, search_scale=a.search_scale, grid_dims=dims) as p:
-        p.solve()
+        if not a.no_solve:
+            p.solve()
         t = p.timings()
 print({kk: (round(v, 3) if isinstance(v, float) else v) for kk, v in t.items()}, (p.info.dimx, p.info.dimy, p.info.dimz))
