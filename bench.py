@@ -44,7 +44,7 @@ sys.path.insert(0, str(ROOT))
 SEED = 20171004
 METRIC = "kNN queries/sec"
 UNIT = "queries/s"
-KERNELS_PER_STEP = 10  # z-band split (2), count, scan, scatter, order, order_big, query (tile, select for handed-over blocks, retry)
+KERNELS_PER_STEP = 12  # z-band split (3: histogram, starts, scatter), count, scan, scatter, order, order_big, query (tile, select for handed-over blocks, retry, short-list retry)
 
 
 def parse():

@@ -85,7 +85,8 @@ class Stats(C.Structure):  # knc_stats
 
 class Timings(C.Structure):  # knc_timings
     _fields_ = [("build_ms", C.c_float), ("solve_ms", C.c_float), ("h2d_ms", C.c_float),
-                ("restarts", C.c_uint), ("max_radius2", C.c_float), ("handed_over_blocks", C.c_uint)]
+                ("restarts", C.c_uint), ("max_radius2", C.c_float), ("handed_over_blocks", C.c_uint),
+                ("second_retries", C.c_uint)]
 
 
 def build(verbose: bool = False) -> Path:
@@ -305,7 +306,8 @@ class KnProblem:
         t = Timings()
         _check(lib().knc_get_timings(self._h, C.byref(t)))
         return {"build_ms": t.build_ms, "solve_ms": t.solve_ms, "h2d_ms": t.h2d_ms, "restarts": t.restarts,
-                "max_radius2": t.max_radius2, "handed_over_blocks": t.handed_over_blocks}
+                "max_radius2": t.max_radius2, "handed_over_blocks": t.handed_over_blocks,
+                "second_retries": t.second_retries}
 
     def _info(self) -> Info:
         i = Info()

@@ -400,6 +400,7 @@ static int solve_finish_impl(knc_problem *p, const char *who) {
     read_timings(p);
     p->t.restarts = diag[0];  // restarts inside the general kernel + queries it took over from the fast one
     p->t.handed_over_blocks = diag[4];  // last chunk's (the counter restarts with every chunk)
+    p->t.second_retries = diag[5];      // likewise
     memcpy(&p->t.max_radius2, &diag[1], sizeof(float));
     p->solved = 1;
     if (verbose()) {
@@ -448,7 +449,7 @@ static int solve_impl(knc_problem *p, unsigned int *out_knn_host, int chunks, co
         const int q0 = c * per, qn = (p->query_count - q0) < per ? (p->query_count - q0) : per;
         if (qn <= 0) break;
         unsigned int *rows = p->pub.d_knearests + (size_t)q0 * p->k;
-        if (c) CU(cudaMemsetAsync(p->d_diag + 3, 0, sizeof(unsigned) * 2, st));  // the retry and block lists start empty
+        if (c) CU(cudaMemsetAsync(p->d_diag + 3, 0, sizeof(unsigned) * 3, st));  // the retry and block lists start empty
         CU(kn_launch_query(p->d_points4, p->pub.d_ptrs, g, p->pub.allocated_points, p->k, p->query_begin + q0, qn,
                            (float)(r0 * r0), rows, p->d_diag, p->d_retry, force_general, p->index_offset, NULL, st));
         if (out_knn_host) {

@@ -99,6 +99,11 @@ struct QueryParams {
     int halo_cells;        // tile kernel: cells staged beyond the block's own x-range on either side
     int bulk_rows_ok;      // tile kernel: the row array is 16-byte aligned, rows may leave as one bulk copy
     float retry_grow;      // retry kernels: factor on the squared radius when a sphere held fewer than k points
+    int *retry_list2;      // queries the second-chance pass of the select kernel could not finish either
+    unsigned int *retry_count2;
+    float retry_radius_sq; // squared radius of the second-chance pass (0: there is none) ...
+    float retry_radius_max_sq;  // ... and the most it may be scaled to for a query at the domain's border (the table's reach)
+    unsigned retry_short;  // a retry list of at most this many queries goes to the warp-per-query kernel
     RowTable tab;
 };
 
@@ -420,10 +425,18 @@ __device__ __forceinline__ void load_records_if(float4 (&c)[kSelChunk], int at, 
     }
 }
 
-// LIST: the blocks to work on are named by P.block_list (what the tile kernel handed over), each resident block takes
-// several in turn; otherwise block b works on queries [b * QB, (b + 1) * QB).
-template <int K_T, int QB, int NET, int CAP, bool LIST>
+// MODE 0: block b works on queries [b * QB, (b + 1) * QB).
+// MODE 1: the blocks to work on are named by P.block_list (what the tile kernel handed over), each resident block takes
+//         several in turn.
+// MODE 2: the SECOND CHANCE of the queries on the retry list, when that list is long (100 M points: 1 % of the queries,
+//         half of them because their first sphere happened to hold fewer than k points, a third because a face of the
+//         domain cut it): thread t of a block takes entry b * QB + t of the list and searches the sphere of
+//         P.retry_radius_sq -- large enough for nearly all of them -- with a buffer that holds it.  Lock step and a sorting
+//         network instead of the general kernel's per-lane loops and insertions, which ran with 8 of 32 lanes active
+//         (profiles/r2_retry_general_100M_k20_*).  What still fails goes to P.retry_list2 and the general kernel.
+template <int K_T, int QB, int NET, int CAP, int MODE>
 __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_constant__ QueryParams P) {
+    constexpr bool LIST = MODE == 1, QLIST = MODE == 2;
     static_assert(K_T > 0 && K_T + 1 <= NET - 8, "select path: k must leave room for new keys in a round");
     static_assert(NET == 32 || NET == 64, "select path: networks exist for 32 and 64 keys");
     constexpr int kSelectCap = CAP, kSelectNet = NET;
@@ -435,13 +448,36 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
     int2 *SP = reinterpret_cast<int2 *>(reinterpret_cast<unsigned int *>(smem) + kSelectCap * QB) + tid;  // [kSpanSlots][QB]
     const int Dx = P.g.Dx, Dy = P.g.Dy, zb = P.g.zb, ze = P.g.ze;
     const float invw = P.g.invwx;
-    const unsigned nlist = LIST ? *P.block_count : gridDim.x;
+    const unsigned qtotal = QLIST ? *P.retry_count : 0u;
+    if (QLIST && qtotal <= P.retry_short) return;  // a short list: the warp-per-query kernel takes it as it is
+    if (QLIST && blockIdx.x == 0 && tid == 0) atomicAdd(P.diag + 0, qtotal);  // counted as restarts
+    const unsigned nlist = QLIST ? (qtotal + QB - 1) / QB : LIST ? *P.block_count : gridDim.x;
   for (unsigned bi = blockIdx.x; bi < nlist; bi += gridDim.x) {
     const long long row0 = (long long)(LIST ? (unsigned)P.block_list[bi] : bi) * QB;
-    const bool valid = row0 + tid < P.query_count;
-    const int q = P.query_begin + (int)min(row0 + tid, (long long)P.query_count - 1);
+    const bool valid = QLIST ? row0 + tid < (long long)qtotal : row0 + tid < P.query_count;
+    const int entry = QLIST ? P.retry_list[min(row0 + tid, (long long)qtotal - 1)] : 0;
+    const int q = QLIST ? (entry & 0x7FFFFFFF) : P.query_begin + (int)min(row0 + tid, (long long)P.query_count - 1);
     const QueryGeom s = query_geom(__ldg(P.pts + q), P.g);
-    const float r2 = P.radius0_sq;
+    // The second chance scales its sphere by the part of it that lies inside the domain: a query on a face of the cube
+    // sees half a sphere and needs twice the volume for the same number of points (an estimate; what makes a row exact
+    // is checked below, as ever).  Rows are walked as far as the widest sphere of the warp needs.
+    float r2 = P.radius0_sq, r2max = P.radius0_sq;
+    if constexpr (QLIST) {
+        // per axis: 1 - the two spherical caps beyond the domain's faces, cap(t) = (1 - t)^2 (2 + t) / 4 at distance t r
+        const float r1 = sqrtf(P.retry_radius_sq), invr = 1.f / r1;
+        auto caps = [&](float p) {
+            const float a = fminf(fmaxf(p, 0.f) * invr, 1.f), b = fminf(fmaxf(1000.f - p, 0.f) * invr, 1.f);
+            return 1.f - 0.25f * ((1.f - a) * (1.f - a) * (2.f + a) + (1.f - b) * (1.f - b) * (2.f + b));
+        };
+        const float vx = caps(s.px), vy = caps(s.py), vz = caps(s.pz);
+        const float visible = fmaxf(vx * vy * vz, 1.f / 64.f);
+        // (an entry without bit 31 had its k points in the first sphere, but too many for the first kernel's buffer,
+        // or a tie of truncated keys: the same sphere again, with this pass's larger buffer and its tie handling)
+        r2 = entry < 0 ? fminf(P.retry_radius_sq * __powf(visible, -2.f / 3.f), P.retry_radius_max_sq) : P.radius0_sq;
+        r2max = r2;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) r2max = fmaxf(r2max, __shfl_xor_sync(0xffffffffu, r2max, d));
+    }
     // Append pointer (shared-memory address of the lane's next free buffer slot).  It is clamped once per
     // chunk, so a chunk may run kSelChunk slots past `wlim`: reaching wlim at all counts as an overflow.
     const unsigned wp0 = (unsigned)__cvta_generic_to_shared(BUF);
@@ -449,7 +485,7 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
     unsigned wp = wp0;
 
     // ---- search the sphere: rows in batches, spans first, then a lock-step stream over them -----------------
-    for (int e0 = 0, e1 = min(kFirstBatch, P.tab.n); e0 < P.tab.n && P.tab.lb2[e0] <= r2;
+    for (int e0 = 0, e1 = min(kFirstBatch, P.tab.n); e0 < P.tab.n && P.tab.lb2[e0] <= r2max;
          e0 = e1, e1 = min(e0 + kNextBatch, P.tab.n)) {
         int nsp = 0;
         for (int e = e0; e < e1; e += 4) {
@@ -573,18 +609,48 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
         if constexpr (NET == 32) { KN_SORT_NETWORK_32(KN_CE) } else { KN_SORT_NETWORK_64(KN_CE) }
 #undef KN_CE
     }
+    // Exact if the truncated distances decide the order.  The second chance (MODE 2) also accepts EQUAL truncated
+    // distances next to each other inside the row and settles each such pair from the exact keys once the row is
+    // written, like the tile kernel; a tie at the k / k+1 border, or three in a row, still go on to the general kernel.
     bool exact = searched;
+    unsigned long long ties = 0;  // bit u: entries u and u + 1 have the same truncated distance
 #pragma unroll
-    for (int u = 0; u < K_T; ++u) exact = exact && (a[u] >> kSlotBits) < (a[u + 1] >> kSlotBits);  // a[K_T] exists: K_T < NET
+    for (int u = 0; u < K_T; ++u) {
+        if constexpr (QLIST) {
+            if ((a[u] >> kSlotBits) == (a[u + 1] >> kSlotBits)) ties |= 1ull << u;  // a[K_T] exists: K_T < NET
+        } else {
+            exact = exact && (a[u] >> kSlotBits) < (a[u + 1] >> kSlotBits);
+        }
+    }
+    if (QLIST) exact = exact && !(ties >> (K_T - 1)) && !(ties & (ties << 1));
     // bit 31 of a retry entry: the sphere held fewer than k points, so the retry must search a larger one
     // (an overflowing buffer or a truncated-key tie is retried with the same radius)
-    if (valid && !exact) P.retry_list[atomicAdd(P.retry_count, 1u)] = q | (cnt < K_T ? (int)0x80000000 : 0);
+    if (valid && !exact) {
+        if (QLIST) P.retry_list2[atomicAdd(P.retry_count2, 1u)] = q | (cnt < K_T ? (int)0x80000000 : 0);
+        else P.retry_list[atomicAdd(P.retry_count, 1u)] = q | (cnt < K_T ? (int)0x80000000 : 0);
+    }
     report_diag(P, s, exact, exact ? __uint_as_float((a[K_T - 1] | kSlotMask)) : 0.f, 0u, tid);
 
     // ---- coalesced row output (through the buffer area: read all k positions, then overwrite) -----------------
     unsigned res[K_T];
 #pragma unroll
     for (int u = 0; u < K_T; ++u) res[u] = exact ? BUF[(a[u] & kSlotMask) * QB] + P.index_offset : KNC_EMPTY;
+    if constexpr (QLIST) {  // scattered rows: each thread writes its own (and only a finished one)
+        if (exact) {
+            unsigned int *out = P.knn + (long long)(q - P.query_begin) * K_T;
+#pragma unroll
+            for (int u = 0; u < K_T; ++u) out[u] = res[u];
+            while (ties) {  // rare, divergent: order each tied pair by its exact (d2, position)
+                const int u = __ffsll((long long)ties) - 1;
+                ties &= ties - 1;
+                const unsigned pa = out[u], pb = out[u + 1];
+                const unsigned long long ka = make_key(__ldg(P.pts + (pa - P.index_offset)), s, (int)pa);
+                const unsigned long long kb = make_key(__ldg(P.pts + (pb - P.index_offset)), s, (int)pb);
+                if (kb < ka) { out[u] = pb; out[u + 1] = pa; }
+            }
+        }
+        continue;
+    }
     // Row stride QB + 1: the transposed read below (consecutive threads walk along a row's k entries, i.e.
     // down a column of OUT) would otherwise hit one bank 16 times over (370 of 2600 L1 wavefronts per warp,
     // profiles/r1_notes.md).
@@ -1083,15 +1149,19 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
     const int Dx = P.g.Dx, Dy = P.g.Dy, zb = P.g.zb, ze = P.g.ze;
     const float invw = P.g.invwx, wmin = fminf(P.g.wy, P.g.wz);
     unsigned long long *L = smem + tid;
-    const long long total = RETRY ? (long long)*P.retry_count : (long long)P.query_count;
+    // which list: the second-chance pass of the select kernel, if it ran, left its own
+    const bool second = RETRY && P.retry_radius_sq > 0.f && *P.retry_count > P.retry_short;
+    const int *list = second ? P.retry_list2 : P.retry_list;
+    const long long total = RETRY ? (long long)(second ? *P.retry_count2 : *P.retry_count) : (long long)P.query_count;
     const long long stride = (long long)gridDim.x * QB;
-    if (RETRY && total <= (long long)gridDim.x * (QB / 32) * kRetryWarpFactor) return;  // a short list: the warp-per-query kernel took it
-    if (RETRY && blockIdx.x == 0 && tid == 0 && total) atomicAdd(P.diag + 0, (unsigned)total);  // counted as restarts
+    if (RETRY && total <= (long long)P.retry_short) return;  // a short list: the warp-per-query kernel took it
+    if (RETRY && blockIdx.x == 0 && tid == 0 && total && !second) atomicAdd(P.diag + 0, (unsigned)total);  // counted as restarts
+    const float retry_r2 = second ? P.retry_radius_sq : P.radius0_sq;  // the sphere these queries were last searched in
 
     for (long long row0 = (long long)blockIdx.x * QB; row0 < total; row0 += stride) {
         const bool valid = row0 + tid < total;
         const long long slot = min(row0 + tid, total - 1);
-        const int entry = RETRY ? P.retry_list[slot] : P.query_begin + (int)slot;
+        const int entry = RETRY ? list[slot] : P.query_begin + (int)slot;
         const int q = EXTERNAL ? -1 : (entry & 0x7FFFFFFF);  // -1: no candidate position equals it, nothing is excluded
         const QueryGeom s = EXTERNAL ? query_geom(make_float4(__ldg(P.ext_queries + 3 * slot), __ldg(P.ext_queries + 3 * slot + 1),
                                                               __ldg(P.ext_queries + 3 * slot + 2), 0.f), P.g)
@@ -1099,7 +1169,7 @@ __global__ void __launch_bounds__(QB) kn_query_general_kernel(const __grid_const
 
         int cnt = 0;
         unsigned long long kth = ~0ull;
-        float r2 = (RETRY && entry < 0) ? P.radius0_sq * P.retry_grow : P.radius0_sq;
+        float r2 = RETRY ? (entry < 0 ? retry_r2 * P.retry_grow : retry_r2) : P.radius0_sq;
         float bound2 = r2;
         bool pruned = false;
         unsigned restarts = 0;
@@ -1218,15 +1288,18 @@ __global__ void __launch_bounds__(QB) kn_query_retry_warp_kernel(const __grid_co
     const int Dx = P.g.Dx, Dy = P.g.Dy, zb = P.g.zb, ze = P.g.ze;
     const float invw = P.g.invwx, wmin = fminf(P.g.wy, P.g.wz);
     unsigned long long *B = smem + (size_t)(tid >> 5) * cap;
-    const long long total = (long long)*P.retry_count;
+    const bool second = P.retry_radius_sq > 0.f && *P.retry_count > P.retry_short;  // see the general kernel
+    const int *list = second ? P.retry_list2 : P.retry_list;
+    const long long total = (long long)(second ? *P.retry_count2 : *P.retry_count);
     const long long warps = (long long)gridDim.x * (QB / 32);
-    if (total > warps * kRetryWarpFactor) return;  // a long list: the general kernel's turn
-    if (blockIdx.x == 0 && tid == 0 && total) atomicAdd(P.diag + 0, (unsigned)total);  // counted as restarts
+    if (total > (long long)P.retry_short) return;  // a long list: the general kernel's turn
+    if (blockIdx.x == 0 && tid == 0 && total && !second) atomicAdd(P.diag + 0, (unsigned)total);  // counted as restarts
+    const float retry_r2 = second ? P.retry_radius_sq : P.radius0_sq;
     for (long long slot = (long long)blockIdx.x * (QB / 32) + (tid >> 5); slot < total; slot += warps) {
-        const int entry = P.retry_list[slot];
+        const int entry = list[slot];
         const int q = entry & 0x7FFFFFFF;
         const QueryGeom s = query_geom(__ldg(P.pts + q), P.g);
-        float r2 = entry < 0 ? P.radius0_sq * 2.25f : P.radius0_sq;
+        float r2 = entry < 0 ? retry_r2 * 2.25f : retry_r2;
         unsigned restarts = 0;
         int cnt = 0;        // keys held (collect mode: inside the sphere; insertion mode: the sorted list)
         bool pruned = false;
@@ -1369,6 +1442,11 @@ cudaError_t launch_retry_warp(const QueryParams &P, unsigned blocks, cudaStream_
     return cudaGetLastError();
 }
 
+// Second chance (select kernel, MODE 2): the sphere is `second_chance_volume` times the first one and the buffer holds
+// its expected count (k + 2.5 sqrt(k) + 2 times that) + 3 sigma + the chunk of overrun room.
+constexpr float second_chance_volume(int k) { return k <= 32 ? 1.6f : 1.3f; }
+constexpr int second_chance_cap(int k) { return k <= 8 ? 48 : k <= 20 ? 80 : k <= 32 ? 108 : 116; }
+
 template <int K_T, int QB>
 cudaError_t launch(const QueryParams &P, bool fast, bool tile_ok, cudaStream_t st) {
     const size_t list_bytes = sizeof(unsigned long long) * (size_t)P.k * QB;
@@ -1402,20 +1480,29 @@ cudaError_t launch(const QueryParams &P, bool fast, bool tile_ok, cudaStream_t s
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
                 if (e != cudaSuccess) return e;
                 const unsigned list_blocks = blocks < 148u * 4u ? blocks : 148u * 4u;  // loops over the block list
-                kn_query_select_kernel<K_T, QB, NET, CAP, true><<<list_blocks, QB, smem, st>>>(P);
+                kn_query_select_kernel<K_T, QB, NET, CAP, 1><<<list_blocks, QB, smem, st>>>(P);
             } else {
-                e = cudaFuncSetAttribute(kn_query_select_kernel<K_T, QB, NET, CAP, false>,
+                e = cudaFuncSetAttribute(kn_query_select_kernel<K_T, QB, NET, CAP, 0>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
                 if (e != cudaSuccess) return e;
-                kn_query_select_kernel<K_T, QB, NET, CAP, false><<<blocks, QB, smem, st>>>(P);
+                kn_query_select_kernel<K_T, QB, NET, CAP, 0><<<blocks, QB, smem, st>>>(P);
+            }
+            if (P.retry_radius_sq > 0.f) {  // second chance of a long retry list, see the kernel (MODE 2)
+                constexpr int NET2 = K_T <= 8 ? 32 : 64, CAP2 = second_chance_cap(K_T);  // (k = 20 with 32 keys a round: a fourth block per SM, yet 1.65 ms instead of 1.38 at 100 M points)
+                const size_t smem2 = (sizeof(unsigned) * CAP2 + sizeof(int2) * kSpanSlots) * QB;
+                e = cudaFuncSetAttribute(kn_query_select_kernel<K_T, QB, NET2, CAP2, 2>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem2);
+                if (e != cudaSuccess) return e;
+                const unsigned want = 148u * (unsigned)(227 * 1024 / (smem2 + 1024));  // loops over the list
+                kn_query_select_kernel<K_T, QB, NET2, CAP2, 2><<<blocks < want ? blocks : want, QB, smem2, st>>>(P);
             }
         }
         e = cudaFuncSetAttribute(kn_query_general_kernel<K_T, QB, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                  (int)list_bytes);
         if (e != cudaSuccess) return e;
-        const unsigned retry_blocks = 148u * 8u;  // fixed: both retry kernels loop over the list, and agree on "short" by this size
+        const unsigned retry_blocks = 148u * 8u;  // both retry kernels loop over the list (which of the two: P.retry_short)
         kn_query_general_kernel<K_T, QB, 1><<<retry_blocks, QB, list_bytes, st>>>(P);
-        e = launch_retry_warp<K_T, QB>(P, retry_blocks, st);  // same grid: the two agree on "short"
+        e = launch_retry_warp<K_T, QB>(P, retry_blocks, st);
         if (e != cudaSuccess) return e;
     } else if (fast) {
         const size_t smem = list_bytes + sizeof(unsigned long long) * (size_t)(kSpanSlots + kQueueSlots) * QB;
@@ -1485,6 +1572,9 @@ cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const Gr
     P.retry_count = d_diag + 3;
     P.block_list = d_retry_list ? d_retry_list + query_count : nullptr;
     P.block_count = d_diag + 4;
+    P.retry_list2 = d_retry_list ? d_retry_list + query_count + (query_count + 31) / 32 + 1 : nullptr;
+    P.retry_count2 = d_diag + 5;
+    P.retry_short = force_general == 6 ? 0u : 148u * 8u * 4u * (unsigned)kRetryWarpFactor;  // algorithm 6: every list counts as long (tests)
     fill_table(P.tab, g.wy, g.wz);
     const float wmin = fminf(g.wy, g.wz), r0 = sqrtf(radius0_sq);
     // The fast kernels search table rows only: usable when every row outside the table is provably
@@ -1498,10 +1588,13 @@ cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const Gr
     const bool tile_ok = force_general != 4 && radius0_sq < reach * reach * kShrink;
     P.halo_cells = (int)ceilf(r0 * kGrow * g.invwx + kMargin * g.invwx + 1e-3f) + 1;  // >= row_x_range's reach, in cells
     P.bulk_rows_ok = ((uintptr_t)d_knn & 15u) == 0;
-    {
-        static float grow_env = -1.f;
-        if (grow_env < 0.f) { const char *e = getenv("KN_RETRY_GROW"); grow_env = e ? (float)atof(e) : 0.f; }
-        P.retry_grow = grow_env > 1.f ? grow_env : 2.25f;
+    P.retry_grow = 2.25f;
+    {   // The second chance exists where the select kernel does (launch<> below) and searches table rows only, like the
+        // first pass: its sphere must stay inside the table too.  algorithm 5 = without it (A/B, tests).
+        const bool has_select = k == 8 || k == 20 || k == 32 || k == 50;
+        const float r1sq = radius0_sq * powf(second_chance_volume(k), 2.f / 3.f);
+        P.retry_radius_sq = (fast && has_select && P.use_select && force_general != 5 && r1sq < beyond * beyond * kShrink) ? r1sq : 0.f;
+        P.retry_radius_max_sq = beyond * beyond * kShrink * 0.999f;
     }
     switch (k) {
         case 8: return launch<8, 128>(P, fast, tile_ok, st);
@@ -1517,7 +1610,8 @@ cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const Gr
 
 size_t kn_retry_ints(int query_count) {
     const size_t q = query_count > 0 ? (size_t)query_count : 1;
-    return q + (q + 31) / 32 + 1;  // retried queries + blocks handed from the tile kernel to the select kernel
+    // retried queries + blocks handed from the tile kernel to the select kernel + queries retried a second time
+    return q + ((size_t)(query_count + 31) / 32 + 1) + q;
 }
 
 // d2 of every stored row entry, with the reference's expression (knearests.cu:125 as compiled) -- the reference

@@ -56,9 +56,10 @@ typedef struct {
     int z_begin, z_end;
     int own_z_begin, own_z_end;
     float search_scale;     /* tuning: multiplies the first-guess search radius; default 1             */
-    int algorithm;          /* 0 = automatic (select/insertion kernel + retry), 1 = general kernel only,
+    int algorithm;          /* 0 = automatic (tile / select / insertion kernel + retry), 1 = general kernel only,
                                2 = insertion kernel for every k, 3 = grid build without the z-band
-                               pre-pass (testing, A/B)                                                  */
+                               pre-pass, 4 = no tile kernel, 5 = no second-chance pass over a long retry
+                               list, 6 = second-chance pass over any retry list (testing, A/B)          */
     int point_stride;       /* floats per input point: 3 (xyz, default) or 4 (xyz + one word that is carried
                                along, see knc_get_tags; e.g. the records knc_slab_route writes)         */
     int grid_dims[3];       /* force the grid resolution per axis (x, y, z; all three > 0).  The reference's grid
@@ -113,6 +114,8 @@ typedef struct {
     float max_radius2;      /* largest squared search radius any query ended with                       */
     unsigned int handed_over_blocks; /* blocks of 128 queries the tile kernel left to the select kernel
                                         (their candidates did not fit its shared-memory tile; diagnostic)  */
+    unsigned int second_retries;     /* queries still unfinished after the second, larger sphere of the select
+                                        kernel (0 when the retry list was short: that pass is skipped; diagnostic) */
 } knc_timings;
 
 /* ---- the hot path -------------------------------------------------------------------------------- */

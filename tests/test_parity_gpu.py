@@ -66,10 +66,13 @@ def test_pts20k_sets_match_reference_kdtree_golden(kn, oracle, pts20k, K):
 
 @pytest.mark.parametrize("n,K,seed", [(11545, 50, 1), (100_000, 20, 2), (300_000, 50, 20171004),
                                       (1_000_000, 20, 20171004), (1_000_000, 8, 1), (500_000, 32, 2)])
-@pytest.mark.parametrize("grid", [{}, REFERENCE_GRID, {"algorithm": 4}], ids=["fast_grid", "reference_grid", "fast_grid_no_tile"])
+@pytest.mark.parametrize("grid", [{}, REFERENCE_GRID, {"algorithm": 4}, {"algorithm": 6}, {"algorithm": 6, **REFERENCE_GRID}],
+                         ids=["fast_grid", "reference_grid", "fast_grid_no_tile", "fast_grid_second_chance", "reference_grid_second_chance"])
 def test_uniform_rows_bit_exact(kn, oracle, n, K, seed, grid):
     """fast_grid: the default grid, tile kernel (+ select kernel for blocks it hands over, + retry kernel);
-    reference_grid: the reference's cube, select kernel; fast_grid_no_tile: the default grid without the tile kernel."""
+    reference_grid: the reference's cube, select kernel; fast_grid_no_tile: the default grid without the tile kernel;
+    *_second_chance: the retry list goes through the select kernel's second, larger sphere whatever its length
+    (by default only a long list does -- clouds of millions of points)."""
     pts = oracle.generate_uniform(n, seed=seed)
     res = run_engine(kn, pts, K, **grid)
     g = assert_layout_equals_oracle(oracle, pts, res, **{k: v for k, v in grid.items() if k != "algorithm"})

@@ -40,7 +40,7 @@ def test_random_clouds_match_the_oracle(kn, oracle, seed):
         n = int(rng.choice([1, 2, 3, 17, 100, 999, 5000, 20000, 60000]))
         k = int(rng.choice([1, 2, 8, 13, 20, 32, 50, 64, 100]))
         density = float(rng.choice([0.0, 0.0, 0.5, 1.0, 3.1, 10.0]))  # 0: the library's own (non-cubic) grid
-        alg = int(rng.choice([0, 0, 0, 1, 2, 4]))
+        alg = int(rng.choice([0, 0, 6, 1, 2, 4]))  # 6: second-chance pass of the select kernel over any retry list
         pts = np.ascontiguousarray(make_cloud(rng, kind, n), np.float32)
         tag = f"seed={seed} case={case} kind={kind} n={n} k={k} density={density} algorithm={alg}"
         with kn.KnProblem(pts, k=k, density=density, algorithm=alg) as p:
