@@ -75,7 +75,8 @@ struct BuildScratch {
     unsigned int *d_bin_tags;    // [n] 4th input words in banded order (large clouds with point_stride 4, else NULL)
 };
 size_t kn_bin_counts_ints(int n);
-#define KN_BIN_MIN_POINTS 20000000  // below this the counters and records stay in L2 anyway (measured: no gain at 14 M)
+#define KN_BIN_MIN_POINTS 4000000  // below this the records being placed stay in L2 anyway (build, ms, with / without the
+                                   // split: 2 M points 0.13 / 0.10, 5 M 0.26 / 0.28, 10 M 0.48 / 0.67, 14 M 0.65 / 1.07, 19 M 0.85 / 1.67)
 size_t kn_build_scratch_tiles(long long cells);
 cudaError_t kn_launch_build(const float *d_in_xyz, int stride, int n, const GridGeom &g, long long cells, int *d_counters,
                             int *d_ptrs, int *d_globcounter, unsigned int *d_permutation, float *d_points3,

@@ -39,7 +39,7 @@ def test_emulated_ranks_reproduce_single_gpu_rows(kn, oracle, world, k, n):
     from cuda_knearests_b200 import slabs
     pts = oracle.generate_uniform(n, seed=20171004)
     dims, zsplit = slabs.grid_and_split(n, world, k)  # the library's own grid with planes in multiples of `world`, as the driver uses it
-    with kn.KnProblem(pts, k=k, grid_dims=dims, algorithm=3 if n > 20_000_000 else 0) as p:  # big case: reference rows without the pre-pass
+    with kn.KnProblem(pts, k=k, grid_dims=dims, algorithm=3 if n > 4_000_000 else 0) as p:  # big case: reference rows without the pre-pass
         p.solve()
         want_rows, want_perm, want_orig = p.get_knearests(), p.get_permutation(), p.get_knearests_original()
     D = dims[2]
