@@ -44,7 +44,7 @@ sys.path.insert(0, str(ROOT))
 SEED = 20171004
 METRIC = "kNN queries/sec"
 UNIT = "queries/s"
-KERNELS_PER_STEP = 12  # z-band split (3: histogram, starts, scatter), count, scan, scatter, order, order_big, query (tile, select for handed-over blocks, retry, short-list retry)
+KERNELS_PER_STEP = 13  # z-band split (3: histogram, starts, scatter), count, scan, scatter, order, order_big, query (tile, select for handed-over blocks, second-chance select, general retry, short-list retry)
 
 
 def parse():
@@ -121,6 +121,11 @@ class ClockSampler:
         self._stop.set()
         if self._t:
             self._t.join()
+
+    def reset(self):
+        """Forget what was sampled so far: called where the timed region starts (the sampler is started before the
+        warm-up steps, because the first NVML calls of a process take ~20 ms and delay the kernel launches next to them)."""
+        self.samples, self.reasons = [], set()
 
     def summary(self):
         s = sorted(self.samples)
@@ -308,14 +313,15 @@ def main_ours(args, rank: int, world: int, local_rank: int):
         p.free()
         return t
 
-    for _ in range(args.warmup):
-        step_device()
-    torch.cuda.synchronize()
-    timings = []
     import gc
-    gc.collect()
-    gc.disable()  # no collection inside the timed region
+    timings = []
     with ClockSampler(local_rank) as clk:
+        for _ in range(args.warmup):
+            step_device()
+        torch.cuda.synchronize()
+        gc.collect()
+        gc.disable()  # no collection inside the timed region
+        clk.reset()
         t0 = time.perf_counter()
         for _ in range(args.steps):
             timings.append(step_device())

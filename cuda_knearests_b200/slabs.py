@@ -405,15 +405,16 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
         r.free()
         return info
 
-    for _ in range(args.warmup):
-        step()
-    dist.barrier()
-    torch.cuda.synchronize()
     infos, step_s = [], []
     import gc
-    gc.collect()
-    gc.disable()  # a collection in the middle of a 5 ms step is 1-2 ms of host time on one rank, and everybody waits for it
-    with ClockSampler(local_rank) as clk:
+    with ClockSampler(local_rank) as clk:  # started before the warm-up: its first NVML calls cost a step ~20 ms (see bench.py)
+        for _ in range(args.warmup):
+            step()
+        dist.barrier()
+        torch.cuda.synchronize()
+        gc.collect()
+        gc.disable()  # a collection in the middle of a 5 ms step is 1-2 ms of host time on one rank, and everybody waits for it
+        clk.reset()
         t0 = time.perf_counter()
         for _ in range(args.steps):
             ts = time.perf_counter()
@@ -511,7 +512,7 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
                 "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
                 "layout": layout,
-                "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 14 * args.steps * world,  # per rank: route 3, build 6 (+3 z-band split when the slab is large), query 2
+                "clocks": clk.summary(), "e2e": e2e, "gpu_launches": 16 * args.steps * world,  # per rank: route 3, build 5 + 3 (z-band split, slabs of 4 M points and more), query 5
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": None, "kernel": "kn_query_tile_kernel + retry kernel (slowest rank)",
                              "kernel_ms": float(allstats[worst][0].item()),
@@ -524,7 +525,7 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
                     "queries": sum(c["queries"] for c in checks), "mismatches": sum(c["mismatches"] for c in checks),
                     "per_rank": checks},
                 "step_ms_rank0": {"min": round(1e3 * min(step_s), 3), "median": round(1e3 * sorted(step_s)[len(step_s) // 2], 3),
-                                  "max": round(1e3 * max(step_s), 3)},
+                                  "max": round(1e3 * max(step_s), 3), "all": [round(1e3 * v, 2) for v in step_s]},
                 "queries_per_rank": queries, "halo_attempts": infos[-1]["attempts"],
                 "phase_ms_rank0_instrumented": {kk: round(v, 3) for kk, v in phase_ms.items()}}
         print(json.dumps(line), flush=True)
