@@ -315,12 +315,12 @@ def main_ours(args, rank: int, world: int, local_rank: int):
 
     import gc
     timings = []
+    gc.collect()
+    gc.disable()  # no collection inside the timed region (nor in the warm-up: the first timed step should find warm caches)
     with ClockSampler(local_rank) as clk:
         for _ in range(args.warmup):
             step_device()
         torch.cuda.synchronize()
-        gc.collect()
-        gc.disable()  # no collection inside the timed region
         clk.reset()
         t0 = time.perf_counter()
         for _ in range(args.steps):

@@ -103,6 +103,7 @@ struct QueryParams {
     unsigned int *retry_count2;
     float retry_radius_sq; // squared radius of the second-chance pass (0: there is none) ...
     float retry_radius_max_sq;  // ... and the most it may be scaled to for a query at the domain's border (the table's reach)
+    float points_per_cell; // the cloud's mean: what the select kernel measures the local density against
     unsigned retry_short;  // a retry list of at most this many queries goes to the warp-per-query kernel
     RowTable tab;
 };
@@ -474,10 +475,31 @@ __global__ void __launch_bounds__(QB) kn_query_select_kernel(const __grid_consta
         // (an entry without bit 31 had its k points in the first sphere, but too many for the first kernel's buffer,
         // or a tie of truncated keys: the same sphere again, with this pass's larger buffer and its tie handling)
         r2 = entry < 0 ? fminf(P.retry_radius_sq * __powf(visible, -2.f / 3.f), P.retry_radius_max_sq) : P.radius0_sq;
-        r2max = r2;
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) r2max = fmaxf(r2max, __shfl_xor_sync(0xffffffffu, r2max, d));
     }
+    // Local density.  The first radius comes from the cloud's MEAN density; inside a cluster its sphere holds many
+    // times k points and overflows every buffer, in a void it holds none.  The points of the query's own row within the
+    // first sphere's reach in x (two pointer loads) say how dense the cloud is HERE against the mean: a row holding
+    // more than 2.5 x its share shrinks the sphere to the volume expected to hold the usual number (+ 20 %), in every
+    // pass; the second chance also grows it for a query whose first sphere came up short in a row holding less than a
+    // quarter of its share, and shrinks
+    // once more for one that overflowed in a dense row.  (On a uniform cloud one row in 10^7 is 2.5 x its mean, one in 10^4
+    // a quarter of it.)
+    // An estimate only: what makes a row exact is checked below, as ever.
+    {
+        const float rx = sqrt_approx(P.radius0_sq) * invw;
+        const int xlo = max(0, min(Dx - 1, (int)floorf(s.tx - rx))), xhi = max(0, min(Dx - 1, (int)floorf(s.tx + rx)));
+        const int own = ((s.ck - zb) * Dy + s.cj) * Dx;
+        const float have_row = (float)(__ldg(P.ptrs + own + xhi + 1) - __ldg(P.ptrs + own + xlo));
+        const float mean_row = (float)(xhi - xlo + 1) * P.points_per_cell;
+        if (have_row > 2.5f * mean_row) {
+            r2 *= __powf((QLIST && entry >= 0 ? 0.7f : 1.2f) * mean_row / have_row, 2.f / 3.f);
+        } else if (QLIST && entry < 0 && have_row < 0.25f * mean_row) {
+            r2 = fminf(r2 * __powf(mean_row / fmaxf(have_row, 1.f), 2.f / 3.f), P.retry_radius_max_sq);
+        }
+    }
+    r2max = r2;  // rows are walked as far as the widest sphere of the warp needs
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) r2max = fmaxf(r2max, __shfl_xor_sync(0xffffffffu, r2max, d));
     // Append pointer (shared-memory address of the lane's next free buffer slot).  It is clamped once per
     // chunk, so a chunk may run kSelChunk slots past `wlim`: reaching wlim at all counts as an overflow.
     const unsigned wp0 = (unsigned)__cvta_generic_to_shared(BUF);
@@ -1572,6 +1594,7 @@ cudaError_t kn_launch_query(const float4 *d_points4, const int *d_ptrs, const Gr
     P.retry_count = d_diag + 3;
     P.block_list = d_retry_list ? d_retry_list + query_count : nullptr;
     P.block_count = d_diag + 4;
+    P.points_per_cell = (float)((double)n / ((double)g.Dx * g.Dy * (g.ze - g.zb)));
     P.retry_list2 = d_retry_list ? d_retry_list + query_count + (query_count + 31) / 32 + 1 : nullptr;
     P.retry_count2 = d_diag + 5;
     P.retry_short = force_general == 6 ? 0u : 148u * 8u * 4u * (unsigned)kRetryWarpFactor;  // algorithm 6: every list counts as long (tests)

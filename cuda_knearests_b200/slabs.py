@@ -407,13 +407,13 @@ def bench_multi(args, rank, world, local_rank, METRIC, UNIT, SEED, workload_conf
 
     infos, step_s = [], []
     import gc
+    gc.collect()
+    gc.disable()  # a collection in the middle of a 5 ms step is 1-2 ms of host time on one rank, and everybody waits for it
     with ClockSampler(local_rank) as clk:  # started before the warm-up: its first NVML calls cost a step ~20 ms (see bench.py)
         for _ in range(args.warmup):
             step()
         dist.barrier()
         torch.cuda.synchronize()
-        gc.collect()
-        gc.disable()  # a collection in the middle of a 5 ms step is 1-2 ms of host time on one rank, and everybody waits for it
         clk.reset()
         t0 = time.perf_counter()
         for _ in range(args.steps):

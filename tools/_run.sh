@@ -1,3 +1,3 @@
-for n in 2000000 5000000 10000000 14200000 19000000; do for m in 1000 2000000000; do
-echo "n $n binmin $m: $(KN_BIN_MIN=$m python profiles/run_case.py --n $n --steps 5 --no-solve 2>&1 | tail -1 | cut -c1-40)"
-done; done
+python -m pytest tests/test_parity_gpu.py tests/test_random_differential_gpu.py -m gpu -x -q 2>&1 | tail -3
+python profiles/extra_cases.py > gpurun_out/r2_extra_cases.txt 2>&1; cat gpurun_out/r2_extra_cases.txt
+echo "k 20: $(python profiles/run_case.py --steps 3 2>&1 | tail -1 | cut -c1-200)"
