@@ -268,6 +268,31 @@ def test_clustered_cloud_overfull_cells_and_restarts(kn, oracle):
     assert r["timings"]["restarts"] > 0
 
 
+@pytest.mark.parametrize("K,algorithm", [(20, 0), (20, 6), (50, 6), (8, 0)])
+def test_clusters_on_a_background_local_density(kn, oracle, K, algorithm):
+    """400 k points: 60 Gaussian clusters (sigma 6) on a 10 % uniform background.  The first radius comes from the MEAN
+    density: inside a cluster its sphere overflows every buffer, in the background it is nearly empty.  The select
+    kernel sizes the sphere by the local density there (algorithm 6: also in its second-chance pass, whatever the
+    length of the retry list); rows must not change."""
+    rng = np.random.default_rng(77)
+    n = 400_000
+    centers = rng.random((60, 3)) * 1000
+    pts = centers[rng.integers(0, 60, n)] + rng.normal(0, 6.0, (n, 3))
+    back = rng.random(n) < 0.1
+    pts[back] = rng.random((int(back.sum()), 3)) * 1000
+    pts = np.ascontiguousarray(np.clip(pts, 0, 999.99), np.float32)
+    r = run_engine(kn, pts, K, algorithm=algorithm)
+    g = assert_layout_equals_oracle(oracle, pts, r)
+    assert np.array_equal(r["knn"], g.knn_exact(K))
+    # queries that are not members of the cloud, on the same data
+    q = np.concatenate([rng.random((2000, 3)).astype(np.float32) * 1000, g.sorted_xyz[::400] + np.float32(0.01)])
+    with kn.KnProblem(pts, k=K, algorithm=algorithm) as p:
+        got, got_d2 = p.query_points(q, with_d2=True)
+    want, want_d2 = oracle.brute_external(g.sorted_xyz, q, K, with_d2=True)
+    assert np.array_equal(got, want)
+    assert np.array_equal(got_d2.view(np.uint32), want_d2.view(np.uint32))
+
+
 def test_planar_and_lattice_clouds_with_many_ties(kn, oracle):
     # integer lattice: massive distance ties, including at the k/k+1 border -> the stated tie-break
     ax = np.arange(0, 40, dtype=np.float32) * 25.0 + 12.5
