@@ -345,7 +345,7 @@ def main_ours(args, rank: int, world: int, local_rank: int):
         except Exception:
             traffic = None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": traffic, "kernel": "kn_query_tile_kernel (+ select kernel for handed-over blocks + retry kernel)", "kernel_ms": solve_ms,
+                "traffic": traffic, "kernel": "kn_query_tile_kernel (+ select kernel for handed-over blocks and as second chance of the retry list + retry kernels)", "kernel_ms": solve_ms,
                 "algorithmic_bytes": algo_bytes, "peak_kind": f"{peak_kind} copy bandwidth (burst)"}
 
     # ---- after the timed region: sampled rows of one more (untimed) pass, checked by the CPU oracle ------------
