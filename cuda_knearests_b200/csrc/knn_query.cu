@@ -784,8 +784,9 @@ __global__ void __launch_bounds__(QB) kn_query_tile_kernel(const __grid_constant
     // rows just below CAP, first span lowest; rows CAP and CAP + 1 hold the terminator.  Spans are consumed as the
     // buffer grows, so the two share the column: the buffer may use every row below the next unread span (a lane that
     // would need more is an overflow and goes to the retry kernel).  That sharing is what lets 5 blocks fit an SM.
-    // (Sharing is used where it buys a fifth block, the 32-key variants; the 64-key variants -- 3 blocks per SM either
-    // way, and 8 % slower with it at k = 50 -- keep their 9 spans in rows of their own above the buffer.)
+    // (Sharing is used where it buys a fifth block, the 32-key variants; the 64-key variants keep their 9 spans in rows
+    // of their own above the buffer: at k = 50 sharing was 8 % slower at the same 3 blocks per SM, and no faster when a
+    // tile of 1920 records made it a fourth block -- 59.9 against 59.4 ms at 100 M points.)
     constexpr bool kShareColumn = NET == 32;
     constexpr int kTermRow = kShareColumn ? CAP : CAP + 18;  // the terminator's rows: kTermRow, kTermRow + 1
     constexpr int kWarpBytes = (kTermRow + 2) * 64;
@@ -1488,11 +1489,13 @@ cudaError_t launch(const QueryParams &P, bool fast, bool tile_ok, cudaStream_t s
             const size_t smem = (sizeof(unsigned) * CAP + sizeof(int2) * kSpanSlots) * QB;
             if (tile_ok) {
                 // the tile kernel's buffer for k <= 20: 60 rows (16-bit entries in a column shared with the span list)
-                constexpr int TCAPB = K_T <= 20 ? 60 : CAP;
+                // k = 32: 84 rows (49 points expected in the sphere, + 4.5 sigma) and a tile of 1880 records let a FOURTH block
+                // share an SM (61 KB -> 56.7 KB per block; 127 registers allow four)
+                constexpr int TCAPB = K_T <= 20 ? 60 : K_T <= 32 ? 84 : CAP;
                 // Tile capacity in records: 9 rows x (the x-extent of QB queries + 2 x reach) at ~1 point per cell is
                 // ~1340 at k = 20, + head and padding (~110), + 4 sigma: the x-extent of 128 consecutive queries varies
                 // by sqrt(128) cells and all 9 rows follow it, sigma ~ 107 records (profiles/r2_notes.md).
-                constexpr int TCAP = K_T <= 20 ? 1760 : 2048;  // 1760 (mean + 3.5 sigma) with 60 buffer rows: 5 blocks share an SM at k <= 20
+                constexpr int TCAP = K_T <= 20 ? 1760 : K_T <= 32 ? 1880 : 2048;  // 1760 (mean + 3.5 sigma) with 60 buffer rows: 5 blocks share an SM at k <= 20
                 const size_t tsmem = (size_t)TCAP * 16 + (size_t)(QB / 32) * ((size_t)(TCAPB + (NET == 32 ? 2 : 20)) * 64);
                 e = cudaFuncSetAttribute(kn_query_tile_kernel<K_T, QB, NET, TCAPB, TCAP>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem);

@@ -1,4 +1,2 @@
-for a in 0 1; do
-ncu --metrics gpu__time_duration.sum --clock-control none -c 30 --csv --log-file gpurun_out/ext_$a.csv python profiles/ext_case.py $a > gpurun_out/ncu1.log 2>&1
-python profiles/launch_summary.py gpurun_out/ext_$a.csv | grep query
-done
+python -m pytest tests/test_parity_gpu.py -m gpu -x -q -k "50 or uniform" 2>&1 | tail -3
+echo "k 50: $(python profiles/run_case.py --steps 3 --k 50 2>&1 | tail -1 | cut -c1-200)"
