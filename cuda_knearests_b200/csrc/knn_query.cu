@@ -1491,11 +1491,11 @@ cudaError_t launch(const QueryParams &P, bool fast, bool tile_ok, cudaStream_t s
                 // the tile kernel's buffer for k <= 20: 60 rows (16-bit entries in a column shared with the span list)
                 // k = 32: 84 rows (49 points expected in the sphere, + 4.5 sigma) and a tile of 1880 records let a FOURTH block
                 // share an SM (61 KB -> 56.7 KB per block; 127 registers allow four)
-                constexpr int TCAPB = K_T <= 20 ? 60 : K_T <= 32 ? 84 : CAP;
+                constexpr int TCAPB = K_T <= 8 ? 40 : K_T <= 20 ? 60 : K_T <= 32 ? 84 : CAP;
                 // Tile capacity in records: 9 rows x (the x-extent of QB queries + 2 x reach) at ~1 point per cell is
                 // ~1340 at k = 20, + head and padding (~110), + 4 sigma: the x-extent of 128 consecutive queries varies
                 // by sqrt(128) cells and all 9 rows follow it, sigma ~ 107 records (profiles/r2_notes.md).
-                constexpr int TCAP = K_T <= 20 ? 1760 : K_T <= 32 ? 1880 : 2048;  // 1760 (mean + 3.5 sigma) with 60 buffer rows: 5 blocks share an SM at k <= 20
+                constexpr int TCAP = K_T <= 8 ? 1672 : K_T <= 20 ? 1760 : K_T <= 32 ? 1880 : 2048;  // 1760 (mean + 3.5 sigma) with 60 buffer rows: 5 blocks share an SM at k <= 20
                 const size_t tsmem = (size_t)TCAP * 16 + (size_t)(QB / 32) * ((size_t)(TCAPB + (NET == 32 ? 2 : 20)) * 64);
                 e = cudaFuncSetAttribute(kn_query_tile_kernel<K_T, QB, NET, TCAPB, TCAP>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tsmem);
