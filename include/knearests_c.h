@@ -57,8 +57,8 @@ typedef struct {
     int own_z_begin, own_z_end;
     float search_scale;     /* tuning: multiplies the first-guess search radius; default 1             */
     int algorithm;          /* 0 = automatic (tile / select / insertion kernel + retry), 1 = general kernel only,
-                               2 = insertion kernel for every k, 3 = grid build without the z-band
-                               pre-pass, 4 = no tile kernel, 5 = no second-chance pass over a long retry
+                               2 = insertion kernel for every k, 3 = grid build without the band
+                               split, 4 = no tile kernel, 5 = no second-chance pass over a long retry
                                list, 6 = second-chance pass over any retry list (testing, A/B)          */
     int point_stride;       /* floats per input point: 3 (xyz, default) or 4 (xyz + one word that is carried
                                along, see knc_get_tags; e.g. the records knc_slab_route writes)         */
@@ -107,7 +107,7 @@ typedef struct {
 /* Device time of the last prepare / solve on this handle, in milliseconds (CUDA events; what the
  * reference prints as "kn_firstbuild: X msec" / "kn_solve: X msec", knearests.cu:200,376). */
 typedef struct {
-    float build_ms;         /* grid build kernels only (count, scan, scatter, order, gather)            */
+    float build_ms;         /* grid build kernels only (band split, count, scan, scatter, order)         */
     float solve_ms;         /* query kernel only                                                        */
     float h2d_ms;           /* host->device copy of the input inside knc_prepare (0 for device input)   */
     unsigned int restarts;  /* queries whose first-guess radius was too small (diagnostic)              */
