@@ -25,7 +25,7 @@
 //  * Candidates are ordered by the 64-bit key bits(d2) << 32 | sorted position: one unsigned compare gives the
 //    total order (d2, position), so the result does not depend on visiting order -- deterministic, and
 //    identical across the three kernels below, across grid densities and across GPUs.
-//  * Four kernels (details at each):
+//  * Five kernels (details at each):
 //      kn_query_tile_kernel     k = 8 / 20 / 32 / 50 on grids whose y/z cells are at least as wide as the first radius
 //                               (the default grid, knc_fast_dims).  A block of 128 consecutive queries stages the
 //                               3 x 3 x-rows of cells around them ONCE in shared memory with bulk asynchronous copies
@@ -34,15 +34,19 @@
 //                               its sphere as 16-bit tile slots, selects like the select kernel below and the block's
 //                               rows leave as one bulk copy shared -> global.
 //      kn_query_select_kernel   k = 8 / 20 / 32 / 50, any grid: the previous generation, still the path for blocks
-//                               whose tile does not fit (clustered clouds) and for cubic grids.  Warp-uniform control flow: span lists, lock-step
+//                               whose tile does not fit (clustered clouds) and for cubic grids, and -- over the retry
+//                               list, with a larger sphere and buffer -- the second chance of the queries the first pass
+//                               could not finish.  Warp-uniform control flow: span lists, lock-step
 //                               streaming of the records through two register buffers, candidates inside the
 //                               sphere are only remembered; one sort-select at the end on 32-bit truncated keys
-//                               (Batcher network in registers) with an exactness guard.
+//                               (Batcher network in registers) with an exactness guard.  Sizes its sphere by the local
+//                               density where the query's own row is far off the cloud's mean.
 //      kn_query_fast_kernel     other k: same streaming, candidates are merged into a sorted list of 64-bit keys
 //                               in shared memory in warp-wide bursts.
 //      kn_query_general_kernel  per-lane nested loops, restarts, rings beyond the row table: exact for any input;
-//                               finishes the few queries the other two hand over (retry list), densely packed,
+//                               finishes the few queries the others hand over (retry list), densely packed,
 //                               serves clouds whose first radius exceeds the table, and external query points.
+//      kn_query_retry_warp_kernel  the same search for a SHORT retry list, one warp per query (small clouds).
 //    (v1 walked rows and candidates in per-lane nested loops for every query: 9 of 32 lanes active on average,
 //    profiles/r1_query_v1_*; the select kernel runs at 31.6.)
 //  * Rows are written through shared memory as one contiguous, coalesced run per block
