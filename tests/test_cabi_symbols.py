@@ -92,3 +92,27 @@ def test_product_never_touches_the_oracle():
             [root / "csrc" / "Makefile"]:
         text = f.read_text()
         assert not re.search(r"\boracle\b|_ref/|libkn_oracle|libref_", text), f"{f} refers to the oracle"
+
+
+def test_ctypes_structs_match_the_header_as_compiled(kn, tmp_path):
+    """The Python door restates knc_options / knc_info / knc_stats / knc_timings by hand: sizes and field offsets are
+    compared with what a C compiler makes of include/knearests_c.h (a field added on one side only would corrupt memory)."""
+    import ctypes as C
+    import subprocess
+    structs = {"knc_options": kn.Options, "knc_info": kn.Info, "knc_stats": kn.Stats, "knc_timings": kn.Timings}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "knearests_c.h"', 'int main(void) {']
+    for cname, cls in structs.items():
+        lines.append(f'  printf("{cname} %zu\\n", sizeof({cname}));')
+        for fname, *_ in cls._fields_:
+            lines.append(f'  printf("{cname}.{fname} %zu\\n", offsetof({cname}, {fname}));')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "abi.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "abi"
+    inc = Path(__file__).resolve().parent.parent / "include"
+    subprocess.run(["gcc", "-std=c99", "-I", str(inc), str(src), "-o", str(exe)], check=True)
+    got = dict(l.split() for l in subprocess.run([str(exe)], capture_output=True, text=True, check=True).stdout.splitlines())
+    for cname, cls in structs.items():
+        assert int(got[cname]) == C.sizeof(cls), cname
+        for fname, *_ in cls._fields_:
+            assert int(got[f"{cname}.{fname}"]) == getattr(cls, fname).offset, f"{cname}.{fname}"
